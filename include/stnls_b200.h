@@ -1,0 +1,147 @@
+/*
+ * stnls_b200.h -- C ABI of the B200-native shifted non-local search + weighted patch sum.
+ *
+ * Drop-in boundary for the hot path of gauenk/stnls.  The reference binds
+ * its kernels through a pybind11 module `stnls_cuda` whose free functions take torch::Tensor
+ * (lib/csrc/pybind.cpp:30-57).  This header is what a maintainer would bind instead: plain
+ * pointers, sizes and a cudaStream_t -- no torch types.  All pointers are DEVICE pointers, all
+ * tensors fp32 unless stated; the caller owns every buffer (the reference's convention:
+ * lib/stnls/search/impl/non_local_search.py:46-49,149-151).  Every call is asynchronous on
+ * `stream`, never synchronises, and returns 0 on success or a negative STNLS_E* code; the last
+ * error text is available from stnls_last_error().
+ *
+ * Internal video layout ("cl"): channels-last, one head per slab,
+ *      (N = B*HD, Tloc, H, W, Fp)   Fp = F_head rounded up to a multiple of 4 (zero padded)
+ * produced by stnls_pack_cl() from the reference's (B,HD,T,F,H,W) or (B,T,HD*F,H,W) tensors
+ * (this replaces the copy `shape_vids` makes, lib/stnls/search/utils.py:178-190) and turned back
+ * by stnls_unpack_cl().  Kernels read/write float4 channel vectors of that layout.
+ *
+ * Frame sharding (multi-GPU): a rank owns query frames [tq0, tq0+Tq) of a clip of T frames and
+ * holds key/value frames [tk0, tk0+Tk) (its own plus the temporal halo).  Single GPU:
+ * tq0=tk0=0, Tq=Tk=T.  All temporal index math uses the global T.
+ */
+#ifndef STNLS_B200_H
+#define STNLS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STNLS_OK 0
+#define STNLS_EINVAL (-1)   /* bad argument (shape / option outside the supported set) */
+#define STNLS_ECUDA (-2)    /* CUDA launch error */
+
+typedef void* stnls_stream_t; /* cudaStream_t */
+
+/* ---- geometry shared by every entry point ------------------------------------------------ */
+typedef struct {
+  int B, HD;          /* batch, heads                                                        */
+  int T;              /* global clip length                                                  */
+  int tq0, Tq;        /* owned query frames [tq0, tq0+Tq)                                    */
+  int tk0, Tk;        /* resident key/value frames [tk0, tk0+Tk)                             */
+  int F, Fp;          /* channels per head, padded channels of the cl layout                 */
+  int qH, qW, kH, kW; /* query / key frame sizes (equal for everything but strideQ searches) */
+  int nH, nW;         /* query grid: (kH-1)/stride0+1, (kW-1)/stride0+1                      */
+} stnls_geom;
+
+/* ---- search options: mirrors the argument lists of
+ *   non_local_search_int_forward / _bilin2d_forward  (lib/csrc/search/non_local_search.cpp:57-62,74-79)
+ *   refinement_int_forward / _bilin2d_forward        (lib/csrc/search/refinement.cpp:39-44,56-62)
+ * `ws,wt,K,Ks,wr` are explicit here (the reference infers them from tensor shapes,
+ * non_local_search_int_kernel.cu:207-212). */
+typedef struct {
+  int ws, wt;          /* NLS: spatial / temporal window.  Refine: unused (0)                 */
+  int Ks, wr;          /* Refine: number of input offsets and refinement window; NLS: 0       */
+  int ps, K;           /* patch size; neighbours kept (K<=0: keep all L, unsorted)            */
+  int stride0, strideQ, dilation;
+  float stride1;
+  int reflect_bounds, full_ws;
+  int patch_offset;    /* 0 if use_adj else -(ps/2)  (impl/non_local_search.py:34)            */
+  int off_Hq, off_Wq;
+  int dist_type;       /* 0 = prod, 1 = l2  (lib/stnls/search/utils.py:225-227)               */
+  int itype_int;       /* 1: int32 flows/inds (non-differentiable), 0: fp32                   */
+  int anchor_self;     /* self_action in {"anchor","anchor_self"}                             */
+  int HD_f;            /* heads of the flows tensor (hd % HD_f indexing)                      */
+  int st_offset;       /* NLS: W_t - flows.size(3) in {0,1}                                   */
+} stnls_search_opts;
+
+const char* stnls_last_error(void);
+int stnls_version(void);
+
+/* ---- layout ------------------------------------------------------------------------------ */
+/* planar (strided) -> cl.  src element (b,hd,t,c,h,w) at src[b*sB + hd*sHD + t*sT + c*sC + h*W + w];
+ * frames t in [t0, t0+Tloc) are packed.  If counts_h/counts_w != NULL every pixel is divided by
+ * (float)(counts_h[h]*counts_w[w]) on the way (gather_add.py:133-134 fused).                  */
+int stnls_pack_cl(float* dst_cl, const float* src, int B, int HD, int t0, int Tloc, int F, int Fp,
+                  int H, int W, int64_t sB, int64_t sHD, int64_t sT, int64_t sC,
+                  const int* counts_h, const int* counts_w, stnls_stream_t stream);
+/* cl -> planar (strided); accumulate != 0 adds into dst instead of overwriting                */
+int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, int t0, int Tloc, int F, int Fp,
+                    int H, int W, int64_t sB, int64_t sHD, int64_t sT, int64_t sC,
+                    int accumulate, stnls_stream_t stream);
+
+/* ---- search forward: kernel + anchor_self + top-K fused ------------------------------------
+ * replaces  stnls_cuda.non_local_search_{int,bilin2d}_forward + stnls_cuda.anchor_self + stnls.nn.topk
+ *           (impl/non_local_search.py:57-126) and
+ *           stnls_cuda.refinement_{int,bilin2d}_forward + anchor_self_refine + topk (impl/refinement.py:56-98)
+ *  q_cl (N,Tq,qH,qW,Fp)  k_cl (N,Tk,kH,kW,Fp)
+ *  flows: NLS    (B,HD_f,Tq,W_t-st_offset,2,nH,nW)   int32 or fp32
+ *         Refine (B,HD_f,Tq,nH,nW,Ks,3)
+ *  dists (B,HD,Tq,nH,nW,Kout)   inds (B,HD,Tq,nH,nW,Kout,3) int32/fp32
+ *      Kout = K>0 ? min(K,L) : L ,  L = (2wt+1)*ws*ws  or  Ks*wr*wr ;  fused top-K needs K<=32
+ *  kselect (B,HD,Tq,nH,nW,Kout) int32 or NULL ; reflect (B,HD_f,Tq,nH,nW,Ks,2) uint8, pre-zeroed, or NULL
+ */
+int stnls_search_forward(const float* q_cl, const float* k_cl, const void* flows,
+                         float* dists, void* inds, int* kselect, uint8_t* reflect,
+                         const stnls_geom* g, const stnls_search_opts* o, stnls_stream_t stream);
+
+/* ---- search backward -------------------------------------------------------------------------
+ * replaces  non_local_search_int_vid_backward / _bilin2d_vid_backward / _bilin2d_vidflows_backward
+ *           (lib/csrc/search/non_local_search.cpp:91-97,112-118,132-138) and
+ *           refinement_bilin2d_vidflows_backward (lib/csrc/search/refinement.cpp:77-86)
+ *  gq_cl (N,Tq,qH,qW,Fp), gk_cl (N,Tk,kH,kW,Fp): pre-zeroed accumulators
+ *  grad_flows: NULL, or pre-zeroed, same shape as flows (NLS layout or refine layout)
+ *  grad_dists (B,HD,Tq,nH,nW,K); grad_inds (…,K,3) (only read when grad_flows != NULL)
+ */
+int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flows,
+                          const float* q_cl, const float* k_cl, const float* flows,
+                          const float* grad_dists, const float* grad_inds, const void* inds,
+                          const int* kselect, const uint8_t* reflect, int K,
+                          const stnls_geom* g, const stnls_search_opts* o, stnls_stream_t stream);
+
+/* ---- weighted patch sum (== NonLocalGatherAdd) ------------------------------------------------
+ * replaces  gather_add_forward / gather_add_int_backward / gather_add_bilin2d_backward
+ *           (lib/csrc/agg/gather_add.cpp:53-57,68-73,86-92)
+ *  v_cl (N,Tk,H,W,Fp); weights (B,HD,Tq,nH,nW,K); flows (B,HD,Tq,nH,nW,K,3) int32/fp32
+ *  out_cl (N,Tq,H,W,Fp): written (gather form, already divided by the patch-overlap counts)
+ *  counts_h (H), counts_w (W): separable overlap counts, counts[h][w] = counts_h[h]*counts_w[w]
+ */
+typedef struct {
+  int ps, K, stride0, dilation, reflect_bounds, patch_offset, itype_int;
+} stnls_agg_opts;
+
+int stnls_wpsum_forward(float* out_cl, const float* v_cl, const float* weights, const void* flows,
+                        const int* counts_h, const int* counts_w,
+                        const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream);
+/*  gout_cl (N,Tq,H,W,Fp): incoming gradient already divided by counts (stnls_pack_cl does it)
+ *  gv_cl (N,Tk,H,W,Fp) pre-zeroed; grad_weights (B,HD,Tq,nH,nW,K) pre-zeroed;
+ *  grad_flows (…,K,3) pre-zeroed or NULL (int)                                                  */
+int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* grad_flows,
+                         const float* gout_cl, const float* v_cl, const float* weights,
+                         const void* flows, const stnls_geom* g, const stnls_agg_opts* o,
+                         stnls_stream_t stream);
+
+/* separable patch-overlap counts (host helper, no GPU): counts_h[h] = #{(nh,pi): nh*stride0 +
+ * dilation*(pi+patch_offset) == h}; equals what gather_add_forward_kernel counts atomically
+ * (lib/csrc/agg/gather_add_kernel.cu:94-97).  Returns the minimum count (0 => reference asserts). */
+int stnls_overlap_counts(int* counts, int H, int nH, int ps, int stride0, int dilation, int patch_offset);
+
+/* ---- halo add: dst[i] += src[i]  (multi-GPU gradient halo reduce) ---------------------------- */
+int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

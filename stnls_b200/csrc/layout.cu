@@ -1,0 +1,123 @@
+// Layout kernels: reference planar video (B,HD,T,F,H,W) / (B,T,HD*F,H,W)  <->  channels-last
+// (B*HD, Tloc, H, W, Fp).  This is the one copy the reference also makes in `shape_vids`
+// (lib/stnls/search/utils.py:178-190, 'b t (HD c) h w -> b HD t c h w' + .contiguous()); here it
+// also pads channels to a multiple of 4 so every kernel moves float4 channel vectors, and (for the
+// aggregation backward) fuses the division by the patch-overlap counts (lib/stnls/agg/gather_add.py:133-134).
+#include "common.cuh"
+
+namespace {
+
+struct LayoutParams {
+  float* cl;
+  float* planar;
+  int HD, t0, Tloc, F, Fp, H, W;
+  int64_t sB, sHD, sT, sC;
+  const int* counts_h;
+  const int* counts_w;
+  int accumulate;
+};
+
+// grid (ceil(W/32), H, N*Tloc), block 256, dynamic smem Fp*33 floats
+template <bool PACK>
+__global__ void __launch_bounds__(256) layout_kernel(const __grid_constant__ LayoutParams P) {
+  extern __shared__ float tile[];  // [Fp][33]
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int w0 = blockIdx.x * 32, h = blockIdx.y;
+  const int tl = blockIdx.z % P.Tloc, n = blockIdx.z / P.Tloc;
+  const int b = n / P.HD, hd = n % P.HD;
+  float* pl = P.planar + (int64_t)b * P.sB + (int64_t)hd * P.sHD + (int64_t)(P.t0 + tl) * P.sT + (int64_t)h * P.W;
+  float* cl = P.cl + ((((int64_t)n * P.Tloc + tl) * P.H + h) * P.W + w0) * P.Fp;
+  const int wn = min(32, P.W - w0);
+  if (PACK) {
+    float inv = 1.f;
+    const bool div = P.counts_h != nullptr;
+    if (div && tx < wn) inv = (float)(P.counts_h[h] * P.counts_w[w0 + tx]);
+    for (int c = ty; c < P.Fp; c += 8) {
+      float v = 0.f;
+      if (c < P.F && tx < wn) {
+        v = pl[(int64_t)c * P.sC + w0 + tx];
+        if (div) v = v / inv;
+      }
+      tile[c * 33 + tx] = v;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
+      int wl = i / P.Fp, c = i - wl * P.Fp;
+      cl[i] = tile[c * 33 + wl];
+    }
+  } else {
+    for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
+      int wl = i / P.Fp, c = i - wl * P.Fp;
+      tile[c * 33 + wl] = cl[i];
+    }
+    __syncthreads();
+    for (int c = ty; c < P.F; c += 8) {
+      if (tx < wn) {
+        float* d = pl + (int64_t)c * P.sC + w0 + tx;
+        float v = tile[c * 33 + tx];
+        *d = P.accumulate ? (*d + v) : v;
+      }
+    }
+  }
+}
+
+__global__ void add_inplace_kernel(float* dst, const float* src, int64_t n) {
+  int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 3 < n) {
+    float4 a = *reinterpret_cast<float4*>(dst + i);
+    float4 b = *reinterpret_cast<const float4*>(src + i);
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    *reinterpret_cast<float4*>(dst + i) = a;
+  } else {
+    for (; i < n; i++) dst[i] += src[i];
+  }
+}
+
+int launch_layout(bool pack, LayoutParams& P, int B, cudaStream_t st, const char* who) {
+  STNLS_REQUIRE(P.cl && P.planar, "%s: null argument", who);
+  STNLS_REQUIRE(P.Fp % 4 == 0 && P.Fp >= P.F && P.F > 0, "%s: Fp must be a multiple of 4 and >= F", who);
+  STNLS_REQUIRE(P.H <= 65535, "%s: H too large", who);
+  int64_t nz = (int64_t)B * P.HD * P.Tloc;
+  if (nz == 0 || P.H == 0 || P.W == 0) return STNLS_OK;
+  STNLS_REQUIRE(nz <= 65535, "%s: B*HD*T too large for one launch", who);
+  dim3 grid((P.W + 31) / 32, P.H, (unsigned)nz);
+  size_t smem = (size_t)P.Fp * 33 * sizeof(float);
+  STNLS_REQUIRE(smem <= 48 * 1024, "%s: too many channels per head (%d)", who, P.F);
+  if (pack) layout_kernel<true><<<grid, 256, smem, st>>>(P);
+  else layout_kernel<false><<<grid, 256, smem, st>>>(P);
+  STNLS_CHECK_LAUNCH(who);
+  return STNLS_OK;
+}
+
+}  // namespace
+
+extern "C" int stnls_pack_cl(float* dst_cl, const float* src, int B, int HD, int t0, int Tloc, int F, int Fp, int H,
+                             int W, int64_t sB, int64_t sHD, int64_t sT, int64_t sC, const int* counts_h,
+                             const int* counts_w, stnls_stream_t stream) {
+  LayoutParams P;
+  P.cl = dst_cl; P.planar = const_cast<float*>(src); P.HD = HD; P.t0 = t0; P.Tloc = Tloc; P.F = F; P.Fp = Fp;
+  P.H = H; P.W = W; P.sB = sB; P.sHD = sHD; P.sT = sT; P.sC = sC; P.counts_h = counts_h; P.counts_w = counts_w;
+  P.accumulate = 0;
+  STNLS_REQUIRE((counts_h == nullptr) == (counts_w == nullptr), "pack_cl: counts_h and counts_w go together");
+  return launch_layout(true, P, B, (cudaStream_t)stream, "pack_cl");
+}
+
+extern "C" int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, int t0, int Tloc, int F, int Fp, int H,
+                               int W, int64_t sB, int64_t sHD, int64_t sT, int64_t sC, int accumulate,
+                               stnls_stream_t stream) {
+  LayoutParams P;
+  P.cl = const_cast<float*>(src_cl); P.planar = dst; P.HD = HD; P.t0 = t0; P.Tloc = Tloc; P.F = F; P.Fp = Fp;
+  P.H = H; P.W = W; P.sB = sB; P.sHD = sHD; P.sT = sT; P.sC = sC; P.counts_h = nullptr; P.counts_w = nullptr;
+  P.accumulate = accumulate;
+  return launch_layout(false, P, B, (cudaStream_t)stream, "unpack_cl");
+}
+
+extern "C" int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t stream) {
+  STNLS_REQUIRE(dst && src, "add_inplace: null argument");
+  if (n <= 0) return STNLS_OK;
+  int64_t nthr = (n + 3) / 4;
+  unsigned blocks = (unsigned)((nthr + 255) / 256);
+  add_inplace_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dst, src, n);
+  STNLS_CHECK_LAUNCH("add_inplace");
+  return STNLS_OK;
+}

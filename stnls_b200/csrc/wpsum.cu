@@ -1,0 +1,248 @@
+// Weighted patch sum (== NonLocalGatherAdd) forward / backward on the channels-last layout.
+// Replaces:
+//   gather_add_forward_kernel          lib/csrc/agg/gather_add_kernel.cu:15-136
+//   gather_add_int_backward_kernel     lib/csrc/agg/gather_add_kernel.cu:201-319
+//   gather_add_bilin2d_backward_kernel lib/csrc/agg/gather_add_kernel.cu:369-514 (+ shared_kernel.cu:773-827)
+// The forward is written as a GATHER (one thread per output pixel and channel quad, looping over the
+// <= ps*ps covering queries and their K neighbours): no atomics, no zero-fill, the division by the
+// patch-overlap count fused in.  The backward keeps grad_weights / grad_flows in registers and
+// scatters grad_v with 16-byte vector REDs.
+#include "common.cuh"
+
+namespace {
+
+struct AggParams {
+  float* out;        // fwd: out_cl ; bwd: gv_cl
+  float* gweights;
+  float* gflows;
+  const float* gout;
+  const float* v;
+  const float* weights;
+  const void* flows;
+  const int* counts_h;
+  const int* counts_w;
+  stnls_geom g;
+  stnls_agg_opts o;
+  int nquad;
+  int64_t nthreads;
+};
+
+template <bool INT>
+__global__ void __launch_bounds__(128) wpsum_fwd_kernel(const __grid_constant__ AggParams P) {
+  const stnls_geom& g = P.g;
+  const stnls_agg_opts& o = P.o;
+  const int H = g.kH, W = g.kW;
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P.nthreads) return;
+  const int c4 = (int)(idx % P.nquad) * 4;
+  int64_t r = idx / P.nquad;
+  const int w = (int)(r % W); r /= W;
+  const int h = (int)(r % H); r /= H;
+  const int tl = (int)(r % g.Tq); r /= g.Tq;
+  const int n = (int)r;
+  const int t = tl + g.tq0;
+  const int64_t vfs = (int64_t)H * W * g.Fp;
+  const float* vb = P.v + (int64_t)n * g.Tk * vfs + c4;
+  float4 acc = f4zero();
+  for (int pi = 0; pi < o.ps; pi++) {
+    const int d = o.dilation * (pi + o.patch_offset);
+    const int hq = h - d;
+    if (hq < 0 || (hq % o.stride0) != 0) continue;
+    const int nh = hq / o.stride0;
+    if (nh >= g.nH) continue;
+    for (int pj = 0; pj < o.ps; pj++) {
+      const int e = o.dilation * (pj + o.patch_offset);
+      const int wq = w - e;
+      if (wq < 0 || (wq % o.stride0) != 0) continue;
+      const int nw = wq / o.stride0;
+      if (nw >= g.nW) continue;
+      const int64_t qb = ((((int64_t)n * g.Tq + tl) * g.nH + nh) * g.nW + nw) * o.K;
+      for (int ki = 0; ki < o.K; ki++) {
+        const float weight = P.weights[qb + ki];
+        if (INT) {
+          const int* f = reinterpret_cast<const int*>(P.flows) + (qb + ki) * 3;
+          int n0 = t + f[0], n1 = hq + f[1], n2 = wq + f[2];
+          if (!((abs(n1) < 1e7) && (abs(n2) < 1e7))) continue;
+          n0 = bnd(n0, g.T); n1 = bnd(n1, H); n2 = bnd(n2, W);
+          n1 += d; n2 += e;
+          if (o.reflect_bounds) { n1 = bnd(n1, H); n2 = bnd(n2, W); }
+          if (!(inb(n0, g.T) && inb(n1, H) && inb(n2, W))) continue;
+          const float4 pix = ldg4(vb + (int64_t)(n0 - g.tk0) * vfs + ((int64_t)n1 * W + n2) * g.Fp);
+          acc.x += weight * pix.x; acc.y += weight * pix.y; acc.z += weight * pix.z; acc.w += weight * pix.w;
+        } else {
+          const float* f = reinterpret_cast<const float*>(P.flows) + (qb + ki) * 3;
+          float n0 = (float)t + f[0], n1 = (float)hq + f[1], n2 = (float)wq + f[2];
+          if (!((fabsf(n1) < 1e7) && (fabsf(n2) < 1e7))) continue;
+          n0 = bnd(n0, g.T); n1 = bnd(n1, H); n2 = bnd(n2, W);
+          n1 += (float)d; n2 += (float)e;
+          if (o.reflect_bounds) { n1 = bnd(n1, H); n2 = bnd(n2, W); }
+          if (!(inb(n0, g.T) && inb(n1, H) && inb(n2, W))) continue;
+          const Taps tp = make_taps(n1, n2, H, W);
+          const float4 pix = interp4(vb - c4 + (int64_t)((int)n0 - g.tk0) * vfs, tp, W, g.Fp, c4);
+          acc.x += weight * pix.x; acc.y += weight * pix.y; acc.z += weight * pix.z; acc.w += weight * pix.w;
+        }
+      }
+    }
+  }
+  const float cnt = (float)(P.counts_h[h] * P.counts_w[w]);
+  float4 o4 = make_float4(acc.x / cnt, acc.y / cnt, acc.z / cnt, acc.w / cnt);
+  *reinterpret_cast<float4*>(P.out + (((int64_t)n * g.Tq + tl) * H + h) * W * g.Fp + (int64_t)w * g.Fp + c4) = o4;
+}
+
+template <bool INT>
+__global__ void __launch_bounds__(128) wpsum_bwd_kernel(const __grid_constant__ AggParams P) {
+  const stnls_geom& g = P.g;
+  const stnls_agg_opts& o = P.o;
+  const int H = g.kH, W = g.kW;
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P.nthreads) return;
+  const int c4 = (int)(idx % P.nquad) * 4;
+  const int64_t wq = idx / P.nquad;
+  int64_t r = wq;
+  const int nw = (int)(r % g.nW); r /= g.nW;
+  const int nh = (int)(r % g.nH); r /= g.nH;
+  const int tl = (int)(r % g.Tq); r /= g.Tq;
+  const int n = (int)r;
+  const int t = tl + g.tq0;
+  const int rh = (nh * o.stride0) % H, rw = (nw * o.stride0) % W;
+  const int64_t vfs = (int64_t)H * W * g.Fp;
+  const float* vb = P.v + (int64_t)n * g.Tk * vfs + c4;
+  float* gvb = P.out + (int64_t)n * g.Tk * vfs + c4;
+  const float* gof = P.gout + ((int64_t)n * g.Tq + tl) * vfs + c4;
+  for (int ki = 0; ki < o.K; ki++) {
+    const int64_t oi = wq * o.K + ki;
+    const float weight = P.weights[oi];
+    float accw = 0.f, fh = 0.f, fw = 0.f;
+    if (INT) {
+      const int* f = reinterpret_cast<const int*>(P.flows) + oi * 3;
+      int n0 = t + f[0], c1 = rh + f[1], c2 = rw + f[2];
+      if (!((abs(c1) < 1e7) && (abs(c2) < 1e7))) continue;
+      n0 = bnd(n0, g.T); c1 = bnd(c1, H); c2 = bnd(c2, W);
+      if (!inb(n0, g.T)) continue;
+      const float* vf = vb + (int64_t)(n0 - g.tk0) * vfs;
+      float* gvf = gvb + (int64_t)(n0 - g.tk0) * vfs;
+      for (int pi = 0; pi < o.ps; pi++) {
+        const int d = o.dilation * (pi + o.patch_offset);
+        const int r1 = rh + d;
+        int n1 = c1 + d;
+        if (o.reflect_bounds) n1 = bnd(n1, H);
+        if (!(inb(r1, H) && inb(n1, H))) continue;
+        for (int pj = 0; pj < o.ps; pj++) {
+          const int e = o.dilation * (pj + o.patch_offset);
+          const int r2 = rw + e;
+          int n2 = c2 + e;
+          if (o.reflect_bounds) n2 = bnd(n2, W);
+          if (!(inb(r2, W) && inb(n2, W))) continue;
+          const float4 gr = ldg4(gof + ((int64_t)r1 * W + r2) * g.Fp);
+          const int64_t vo = ((int64_t)n1 * W + n2) * g.Fp;
+          const float4 pv = ldg4(vf + vo);
+          red_add4(gvf + vo, f4scale(gr, weight));
+          accw += gr.x * pv.x + gr.y * pv.y + gr.z * pv.z + gr.w * pv.w;
+        }
+      }
+    } else {
+      const float* f = reinterpret_cast<const float*>(P.flows) + oi * 3;
+      float n0 = (float)t + f[0], c1 = (float)rh + f[1], c2 = (float)rw + f[2];
+      if (!((fabsf(c1) < 1e7) && (fabsf(c2) < 1e7))) continue;
+      n0 = bnd(n0, g.T);
+      const int sH0 = inb(c1, H) ? 1 : -1;
+      c1 = bnd(c1, H);
+      const int sW0 = inb(c2, W) ? 1 : -1;
+      c2 = bnd(c2, W);
+      if (!inb(n0, g.T)) continue;
+      const int nti = (int)n0;
+      const float* vf = vb + (int64_t)(nti - g.tk0) * vfs;
+      float* gvf = gvb + (int64_t)(nti - g.tk0) * vfs;
+      for (int pi = 0; pi < o.ps; pi++) {
+        const int d = o.dilation * (pi + o.patch_offset);
+        const int r1 = rh + d;
+        float n1 = c1 + (float)d;
+        const int signH = inb(n1, H) ? sH0 : -sH0;
+        if (o.reflect_bounds) n1 = bnd(n1, H);
+        if (!(inb(r1, H) && inb(n1, H))) continue;
+        for (int pj = 0; pj < o.ps; pj++) {
+          const int e = o.dilation * (pj + o.patch_offset);
+          const int r2 = rw + e;
+          float n2 = c2 + (float)e;
+          const int signW = inb(n2, W) ? sW0 : -sW0;
+          if (o.reflect_bounds) n2 = bnd(n2, W);
+          if (!(inb(r2, W) && inb(n2, W))) continue;
+          const float4 gr = ldg4(gof + ((int64_t)r1 * W + r2) * g.Fp);
+          const float4 wg = f4scale(gr, weight);
+          const Taps tp = make_taps(n1, n2, H, W);
+          float aH = 0.f, aW = 0.f;
+#pragma unroll
+          for (int ix = 0; ix < 2; ix++) {
+#pragma unroll
+            for (int jx = 0; jx < 2; jx++) {
+              if (!tp.vh[ix] || !tp.vw[jx]) continue;
+              const int64_t vo = ((int64_t)tp.h[ix] * W + tp.w[jx]) * g.Fp;
+              const float4 pv = ldg4(vf + vo);
+              const float dot = gr.x * pv.x + gr.y * pv.y + gr.z * pv.z + gr.w * pv.w;
+              accw += tp.gh[ix] * tp.gw[jx] * dot;
+              aW += (jx == 0) ? -tp.gh[ix] * dot : tp.gh[ix] * dot;
+              aH += (ix == 0) ? -tp.gw[jx] * dot : tp.gw[jx] * dot;
+              red_add4(gvf + vo, f4scale(wg, tp.gh[ix] * tp.gw[jx]));
+            }
+          }
+          fh += weight * aH * signH;
+          fw += weight * aW * signW;
+        }
+      }
+    }
+    atomicAdd(P.gweights + oi, accw);
+    if (!INT) {
+      atomicAdd(P.gflows + oi * 3 + 1, fh);
+      atomicAdd(P.gflows + oi * 3 + 2, fw);
+    }
+  }
+}
+
+int agg_check(const stnls_geom* g, const stnls_agg_opts* o, const char* who) {
+  STNLS_REQUIRE(g && o, "%s: null argument", who);
+  STNLS_REQUIRE(g->Fp % 4 == 0 && g->Fp >= g->F, "%s: Fp must be a multiple of 4 and >= F", who);
+  STNLS_REQUIRE(g->qH == g->kH && g->qW == g->kW, "%s: output size must equal input size", who);
+  STNLS_REQUIRE(o->ps > 0 && o->stride0 > 0 && o->K >= 0, "%s: bad ps/stride0/K", who);
+  return STNLS_OK;
+}
+
+}  // namespace
+
+extern "C" int stnls_wpsum_forward(float* out_cl, const float* v_cl, const float* weights, const void* flows,
+                                   const int* counts_h, const int* counts_w, const stnls_geom* g,
+                                   const stnls_agg_opts* o, stnls_stream_t stream) {
+  if (int rc = agg_check(g, o, "wpsum_forward")) return rc;
+  STNLS_REQUIRE(out_cl && v_cl && weights && flows && counts_h && counts_w, "wpsum_forward: null argument");
+  AggParams P = {};
+  P.out = out_cl; P.v = v_cl; P.weights = weights; P.flows = flows; P.counts_h = counts_h; P.counts_w = counts_w;
+  P.g = *g; P.o = *o; P.nquad = g->Fp / 4;
+  P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->kH * g->kW * P.nquad;
+  if (P.nthreads == 0) return STNLS_OK;
+  STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_forward: too many threads for one launch");
+  unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (o->itype_int) wpsum_fwd_kernel<true><<<blocks, 128, 0, st>>>(P);
+  else wpsum_fwd_kernel<false><<<blocks, 128, 0, st>>>(P);
+  STNLS_CHECK_LAUNCH("wpsum_forward");
+  return STNLS_OK;
+}
+
+extern "C" int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* grad_flows, const float* gout_cl,
+                                    const float* v_cl, const float* weights, const void* flows,
+                                    const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream) {
+  if (int rc = agg_check(g, o, "wpsum_backward")) return rc;
+  STNLS_REQUIRE(gv_cl && grad_weights && gout_cl && v_cl && weights && flows, "wpsum_backward: null argument");
+  STNLS_REQUIRE(o->itype_int || grad_flows, "wpsum_backward: grad_flows required for itype float");
+  AggParams P = {};
+  P.out = gv_cl; P.gweights = grad_weights; P.gflows = grad_flows; P.gout = gout_cl; P.v = v_cl;
+  P.weights = weights; P.flows = flows; P.g = *g; P.o = *o; P.nquad = g->Fp / 4;
+  P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->nH * g->nW * P.nquad;
+  if (P.nthreads == 0 || o->K == 0) return STNLS_OK;
+  STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_backward: too many threads for one launch");
+  unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (o->itype_int) wpsum_bwd_kernel<true><<<blocks, 128, 0, st>>>(P);
+  else wpsum_bwd_kernel<false><<<blocks, 128, 0, st>>>(P);
+  STNLS_CHECK_LAUNCH("wpsum_backward");
+  return STNLS_OK;
+}

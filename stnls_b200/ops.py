@@ -1,0 +1,171 @@
+"""Thin tensor-level wrappers over the C ABI (pointer extraction, shape checks, allocation).
+
+Every function requires CUDA tensors and raises otherwise -- there is no CPU path.
+"""
+import ctypes
+
+import torch as th
+
+from . import _C
+from ._C import AggOpts, Geom, SearchOpts
+
+MAX_FUSED_K = 32
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _stream():
+    return ctypes.c_void_p(th.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("stnls_b200: tensors must be CUDA tensors (there is no CPU path)")
+
+
+def padded_channels(F):
+    return (F + 3) // 4 * 4
+
+
+def _planar_strides(vid, nheads):
+    """(B,T,HD*F,H,W) or (B,HD,T,F,H,W) -> B,HD,T,F,H,W + element strides sB,sHD,sT,sC"""
+    if vid.dim() not in (5, 6):
+        raise ValueError("Must be 5 or 6 dims.")
+    if vid.dtype != th.float32:
+        raise TypeError(f"stnls_b200 supports float32 videos only (got {vid.dtype})")
+    H, W = vid.shape[-2:]
+    if vid.stride(-1) != 1 or vid.stride(-2) != W:
+        vid = vid.contiguous()
+    if vid.dim() == 5:
+        B, T, Fc = vid.shape[:3]
+        if Fc % nheads != 0:
+            raise ValueError("must be multiple of each other.")
+        F = Fc // nheads
+        s = (vid.stride(0), F * vid.stride(2), vid.stride(1), vid.stride(2))
+        return vid, (B, nheads, T, F, H, W), s
+    B, HD, T, F = vid.shape[:4]
+    if HD != nheads:
+        raise ValueError(f"video has {HD} heads, expected {nheads}")
+    return vid, (B, HD, T, F, H, W), (vid.stride(0), vid.stride(1), vid.stride(2), vid.stride(3))
+
+
+def pack_cl(vid, nheads, t0=0, Tloc=None, counts=None):
+    """planar video -> channels-last (B*HD, Tloc, H, W, Fp); optional fused divide by counts."""
+    _need_cuda(vid)
+    vid, (B, HD, T, F, H, W), (sB, sHD, sT, sC) = _planar_strides(vid, nheads)
+    Tloc = T - t0 if Tloc is None else Tloc
+    Fp = padded_channels(F)
+    out = th.empty((B * HD, Tloc, H, W, Fp), device=vid.device, dtype=th.float32)
+    ch, cw = (None, None) if counts is None else counts
+    _C.check(_C.lib().stnls_pack_cl(_ptr(out), _ptr(vid), B, HD, t0, Tloc, F, Fp, H, W,
+                                    sB, sHD, sT, sC, _ptr(ch), _ptr(cw), _stream()))
+    return out
+
+
+def unpack_cl(cl, shape, nheads, t0=0, out=None, accumulate=False):
+    """channels-last -> planar tensor of `shape` ((B,T,HD*F,H,W) or (B,HD,T,F,H,W))."""
+    _need_cuda(cl)
+    if out is None:
+        out = th.empty(shape, device=cl.device, dtype=th.float32)
+    _, (B, HD, T, F, H, W), (sB, sHD, sT, sC) = _planar_strides(out, nheads)
+    Tloc, Fp = cl.shape[1], cl.shape[4]
+    assert cl.shape[0] == B * HD and cl.shape[2] == H and cl.shape[3] == W and cl.is_contiguous()
+    _C.check(_C.lib().stnls_unpack_cl(_ptr(out), _ptr(cl), B, HD, t0, Tloc, F, Fp, H, W,
+                                      sB, sHD, sT, sC, int(accumulate), _stream()))
+    return out
+
+
+def make_geom(B, HD, T, F, qH, qW, kH, kW, stride0, tq0=0, Tq=None, tk0=0, Tk=None):
+    Tq = T if Tq is None else Tq
+    Tk = T if Tk is None else Tk
+    return Geom(B, HD, T, tq0, Tq, tk0, Tk, F, padded_channels(F), qH, qW, kH, kW,
+                (kH - 1) // stride0 + 1, (kW - 1) // stride0 + 1)
+
+
+def search_forward(q_cl, k_cl, flows, geom, opts):
+    """Fused search + anchor + top-K.  Returns dists, inds, kselect, reflect (last two refine-float only)."""
+    _need_cuda(q_cl, k_cl, flows)
+    g, o = geom, opts
+    refine = o.wr > 0
+    L = (o.Ks * o.wr * o.wr) if refine else ((2 * o.wt + 1) * o.ws * o.ws)
+    Kout = min(o.K, L) if o.K > 0 else L
+    dev = q_cl.device
+    itype = th.int32 if o.itype_int else th.float32
+    dists = th.empty((g.B, g.HD, g.Tq, g.nH, g.nW, Kout), device=dev, dtype=th.float32)
+    inds = th.empty((g.B, g.HD, g.Tq, g.nH, g.nW, Kout, 3), device=dev, dtype=itype)
+    kselect = reflect = None
+    if refine and not o.itype_int:
+        kselect = th.empty(dists.shape, device=dev, dtype=th.int32)
+        reflect = th.zeros(tuple(flows.shape[:-1]) + (2,), device=dev, dtype=th.uint8)
+    assert flows.is_contiguous() and flows.dtype == itype
+    _C.check(_C.lib().stnls_search_forward(_ptr(q_cl), _ptr(k_cl), _ptr(flows), _ptr(dists), _ptr(inds),
+                                           _ptr(kselect), _ptr(reflect), ctypes.byref(g), ctypes.byref(o),
+                                           _stream()))
+    return dists, inds, kselect, reflect
+
+
+def search_backward(q_cl, k_cl, flows, grad_dists, grad_inds, inds, kselect, reflect, geom, opts,
+                    flows_grad):
+    """Returns gq_cl, gk_cl, grad_flows (or None)."""
+    _need_cuda(q_cl, k_cl, grad_dists, inds)
+    g, o = geom, opts
+    gq = th.zeros_like(q_cl)
+    gk = th.zeros_like(k_cl)
+    gflows = None
+    grad_dists = grad_dists.contiguous().float()
+    K = grad_dists.shape[-1]
+    inds = inds.contiguous()
+    if flows_grad:
+        gflows = th.zeros_like(flows, dtype=th.float32)
+        grad_inds = grad_inds.contiguous().float()
+        if reflect is not None:
+            reflect = reflect.to(th.uint8).contiguous()
+    _C.check(_C.lib().stnls_search_backward(_ptr(gq), _ptr(gk), _ptr(gflows), _ptr(q_cl), _ptr(k_cl),
+                                            _ptr(flows if flows_grad else None), _ptr(grad_dists),
+                                            _ptr(grad_inds if flows_grad else None), _ptr(inds),
+                                            _ptr(kselect), _ptr(reflect), K,
+                                            ctypes.byref(g), ctypes.byref(o), _stream()))
+    return gq, gk, gflows
+
+
+_COUNT_CACHE = {}
+
+
+def overlap_counts(H, nH, ps, stride0, dilation, patch_offset, device):
+    """Separable patch-overlap counts (int32 device vector) + their minimum."""
+    key = (H, nH, ps, stride0, dilation, patch_offset, str(device))
+    if key not in _COUNT_CACHE:
+        buf = (ctypes.c_int * H)()
+        mn = _C.lib().stnls_overlap_counts(buf, H, nH, ps, stride0, dilation, patch_offset)
+        _COUNT_CACHE[key] = (th.tensor(list(buf), dtype=th.int32, device=device), mn)
+    return _COUNT_CACHE[key]
+
+
+def wpsum_forward(v_cl, weights, flows, counts, geom, opts):
+    _need_cuda(v_cl, weights, flows)
+    g = geom
+    out = th.empty((g.B * g.HD, g.Tq, g.kH, g.kW, g.Fp), device=v_cl.device, dtype=th.float32)
+    _C.check(_C.lib().stnls_wpsum_forward(_ptr(out), _ptr(v_cl), _ptr(weights), _ptr(flows),
+                                          _ptr(counts[0]), _ptr(counts[1]),
+                                          ctypes.byref(g), ctypes.byref(opts), _stream()))
+    return out
+
+
+def wpsum_backward(gout_cl, v_cl, weights, flows, geom, opts):
+    _need_cuda(gout_cl, v_cl, weights, flows)
+    gv = th.zeros_like(v_cl)
+    gw = th.zeros_like(weights)
+    gf = None if opts.itype_int else th.zeros(flows.shape, device=flows.device, dtype=th.float32)
+    _C.check(_C.lib().stnls_wpsum_backward(_ptr(gv), _ptr(gw), _ptr(gf), _ptr(gout_cl), _ptr(v_cl),
+                                           _ptr(weights), _ptr(flows),
+                                           ctypes.byref(geom), ctypes.byref(opts), _stream()))
+    return gv, gw, gf
+
+
+def add_inplace(dst, src):
+    assert dst.is_contiguous() and src.is_contiguous() and dst.numel() == src.numel()
+    _C.check(_C.lib().stnls_add_inplace(_ptr(dst), _ptr(src), dst.numel(), _stream()))
+    return dst

@@ -1,0 +1,59 @@
+"""Shared helpers for the parity tests."""
+import torch as th
+
+
+def make_vids(B, T, F, H, W, seed=0, n=3):
+    g = th.Generator().manual_seed(seed)
+    return [th.randn(B, T, F, H, W, generator=g) for _ in range(n)]
+
+
+def make_flows(B, HD_f, T, nF, nH, nW, kind, seed=1):
+    """kind 'int': clamp(10*randn,-3,3).round()  (tests/search/test_non_local_search_int.py:79-80)
+       kind 'float': rand/2 + randint(-3,3) + 0.2 (tests/search/test_non_local_search_bilin2d.py:268-269)"""
+    g = th.Generator().manual_seed(seed)
+    shape = (B, HD_f, T, nF, 2, nH, nW)
+    if kind == "int":
+        return th.clamp(10 * th.randn(shape, generator=g), -3, 3).round()
+    if kind == "zero":
+        return th.zeros(shape)
+    return th.rand(shape, generator=g) / 2 + th.randint(-3, 3, shape, generator=g) + 0.2
+
+
+def assert_topk_equal(d, i, d_ref, i_ref, exact, atol=1e-4, rtol=1e-4, what=""):
+    """Compare (dists, inds) of a top-K search.  exact: bit-equal dists and equal indices.
+    Otherwise dists within tolerance and indices equal wherever the neighbouring distances are
+    separated by more than the tolerance (near-ties may legitimately swap)."""
+    d, i, d_ref, i_ref = d.cpu(), i.cpu(), d_ref.cpu(), i_ref.cpu()
+    assert d.shape == d_ref.shape, (what, d.shape, d_ref.shape)
+    assert i.shape == i_ref.shape, (what, i.shape, i_ref.shape)
+    if exact:
+        same = (d == d_ref) | (th.isnan(d) & th.isnan(d_ref))
+        assert bool(same.all()), f"{what}: dists differ at {int((~same).sum())} of {d.numel()} entries"
+        bad = (i != i_ref).any(-1)
+        assert not bool(bad.any()), f"{what}: inds differ at {int(bad.sum())} of {bad.numel()} entries"
+        return
+    fin = th.isfinite(d_ref)
+    assert bool((th.isfinite(d) == fin).all()), f"{what}: finite masks differ"
+    assert th.allclose(d[fin], d_ref[fin], atol=atol, rtol=rtol), \
+        f"{what}: dists max err {float((d[fin]-d_ref[fin]).abs().max())}"
+    assert bool((d[~fin] == d_ref[~fin]).all())
+    tol = atol + rtol * d_ref.abs()
+    gap_prev = th.full_like(d_ref, float("inf"))
+    gap_next = th.full_like(d_ref, float("inf"))
+    gap_prev[..., 1:] = (d_ref[..., 1:] - d_ref[..., :-1]).abs()
+    gap_next[..., :-1] = gap_prev[..., 1:]
+    clear = fin & (gap_prev > 4 * tol) & (gap_next > 4 * tol)
+    diff = (i.float() - i_ref.float()).abs().amax(-1)
+    bad = clear & (diff > 1e-3)
+    assert not bool(bad.any()), f"{what}: inds differ at {int(bad.sum())} clearly separated entries"
+    frac = float(clear.float().mean())
+    assert frac > 0.5, f"{what}: too few clearly separated entries to check inds ({frac})"
+
+
+def assert_close(a, b, atol, rtol, what=""):
+    a, b = a.detach().cpu().float(), b.detach().cpu().float()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    err = (a - b).abs()
+    ok = err <= atol + rtol * b.abs()
+    assert bool(ok.all()), f"{what}: {int((~ok).sum())}/{ok.numel()} off, max err {float(err.max())}, " \
+                           f"ref scale {float(b.abs().max())}"
