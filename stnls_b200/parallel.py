@@ -1,1 +1,174 @@
-"""Frame-sharded multi-GPU execution (placeholder filled in below)."""
+"""Frame-sharded multi-GPU execution: one process per GPU, frames of a clip partitioned contiguously
+across ranks, and ONE exchange step -- the temporal halo of k (search) and v (aggregation).
+
+The reference has no distributed layer at all.  The path shards naturally: every
+query only touches frames of its own clip inside its temporal window
+(lib/csrc/shared_kernel.cu:300-312), so q, flows, dists, inds, weights and the output are owned and
+never exchanged; k / v need frames [t_min(t), t_max(t)] for the owned t (the window is SHIFTED, not
+truncated, at clip ends, so the halo is up to 2*wt frames inward there).  Forward: neighbour ranks
+send halo frames (NCCL send/recv over NVLink, grouped in one batch).  Backward: the same pattern
+reversed, carrying grad_k / grad_v halo slices that are SUMMED into the owner.  No all-reduce, no
+all-gather of full tensors.
+"""
+import torch as th
+import torch.distributed as dist
+
+
+def shard_frames(T, world, rank):
+    """Contiguous, balanced partition of T frames: returns [a, b)."""
+    base, rem = divmod(T, world)
+    a = rank * base + min(rank, rem)
+    return a, a + base + (1 if rank < rem else 0)
+
+
+def time_window(t, T, wt):
+    """[t_min, t_max] searched from frame t (set_time_range_minmax, lib/csrc/shared_kernel.cu:300-305)."""
+    t_shift = min(0, t - wt) + max(0, t + wt - (T - 1))
+    return max(t - wt - t_shift, 0), min(T - 1, t + wt - t_shift)
+
+
+def needed_frames(a, b, T, wt):
+    """Frames of k/v a rank owning [a,b) must hold: union of the windows of its frames, as [fa, fb)."""
+    if b <= a:
+        return a, a
+    lo = min(time_window(t, T, wt)[0] for t in range(a, b))
+    hi = max(time_window(t, T, wt)[1] for t in range(a, b))
+    return lo, hi + 1
+
+
+class ShardPlan:
+    """Who owns what and who needs what, computed identically on every rank (no communication)."""
+
+    def __init__(self, T, wt, world, rank):
+        self.T, self.wt, self.world, self.rank = T, wt, world, rank
+        self.owned = [shard_frames(T, world, r) for r in range(world)]
+        self.need = [needed_frames(a, b, T, wt) for (a, b) in self.owned]
+        self.a, self.b = self.owned[rank]
+        self.fa, self.fb = self.need[rank]
+
+    @property
+    def shard(self):
+        """The `shard=` argument of the search / aggregation modules."""
+        return dict(T=self.T, tq0=self.a, tk0=self.fa)
+
+    def recvs(self, rank=None):
+        """[(src_rank, lo, hi)]: frames [lo,hi) this rank receives from src (its halo)."""
+        r = self.rank if rank is None else rank
+        fa, fb = self.need[r]
+        out = []
+        for s, (a, b) in enumerate(self.owned):
+            lo, hi = max(fa, a), min(fb, b)
+            if s != r and lo < hi:
+                out.append((s, lo, hi))
+        return out
+
+    def sends(self, rank=None):
+        """[(dst_rank, lo, hi)]: owned frames [lo,hi) this rank sends to dst."""
+        r = self.rank if rank is None else rank
+        a, b = self.owned[r]
+        out = []
+        for d, (fa, fb) in enumerate(self.need):
+            lo, hi = max(fa, a), min(fb, b)
+            if d != r and lo < hi:
+                out.append((d, lo, hi))
+        return out
+
+    def halo_bytes(self, frame_bytes):
+        return sum(hi - lo for _, lo, hi in self.recvs()) * frame_bytes
+
+
+def _run_p2p(ops_list):
+    if ops_list:
+        for w in dist.batch_isend_irecv(ops_list):
+            w.wait()
+
+
+def _time_dim(x):
+    return 1 if x.dim() == 5 else 2  # (B,T,F,H,W) or (B,HD,T,F,H,W)
+
+
+def _exchange_forward(x, plan, group):
+    td = _time_dim(x)
+    shape = list(x.shape)
+    shape[td] = plan.fb - plan.fa
+    ext = x.new_empty(shape)
+    ext.narrow(td, plan.a - plan.fa, plan.b - plan.a).copy_(x)
+    p2p, stage = [], []
+    for dst, lo, hi in plan.sends():
+        buf = x.narrow(td, lo - plan.a, hi - lo).contiguous()
+        p2p.append(dist.P2POp(dist.isend, buf, dst, group))
+    for src, lo, hi in plan.recvs():
+        s = list(x.shape)
+        s[td] = hi - lo
+        buf = x.new_empty(s)
+        stage.append((buf, lo, hi))
+        p2p.append(dist.P2POp(dist.irecv, buf, src, group))
+    _run_p2p(p2p)
+    for buf, lo, hi in stage:
+        ext.narrow(td, lo - plan.fa, hi - lo).copy_(buf)
+    return ext
+
+
+def _exchange_backward(gext, plan, group):
+    """Reverse pattern: halo slices of the gradient travel back to their owners and are summed there."""
+    td = _time_dim(gext)
+    gown = gext.narrow(td, plan.a - plan.fa, plan.b - plan.a).contiguous()
+    p2p, stage = [], []
+    for src, lo, hi in plan.recvs():      # frames we borrowed -> give their gradient back
+        buf = gext.narrow(td, lo - plan.fa, hi - lo).contiguous()
+        p2p.append(dist.P2POp(dist.isend, buf, src, group))
+    for dst, lo, hi in plan.sends():      # frames we lent -> receive their gradient
+        s = list(gown.shape)
+        s[td] = hi - lo
+        buf = gown.new_empty(s)
+        stage.append((buf, lo, hi))
+        p2p.append(dist.P2POp(dist.irecv, buf, dst, group))
+    _run_p2p(p2p)
+    for buf, lo, hi in stage:
+        tgt = gown.narrow(td, lo - plan.a, hi - lo)
+        if tgt.is_cuda and tgt.is_contiguous():
+            from . import ops
+            ops.add_inplace(tgt, buf)
+        else:
+            tgt.add_(buf)
+    return gown
+
+
+class HaloExchange(th.autograd.Function):
+    """owned frames [a,b) -> resident frames [fa,fb); differentiable (backward = halo gradient reduce)."""
+
+    @staticmethod
+    def forward(ctx, x, plan, group=None):
+        ctx.plan, ctx.group = plan, group
+        return _exchange_forward(x.contiguous(), plan, group)
+
+    @staticmethod
+    def backward(ctx, gext):
+        return _exchange_backward(gext.contiguous(), ctx.plan, ctx.group), None, None
+
+
+def halo_exchange(x, plan, group=None):
+    if plan.world == 1:
+        return x
+    return HaloExchange.apply(x, plan, group)
+
+
+class ShardedSearchAgg(th.nn.Module):
+    """search -> softmax -> weighted patch sum on this rank's frames; k and v halos exchanged over NCCL.
+
+    q, k, v: the OWNED frames (B,T_own,F,H,W); flows (B,HD_f,T_own,W_t[-1],2,nH,nW) for the owned frames.
+    Returns the owned frames of the aggregated video (B,HD,T_own,F_head,H,W), dists and inds.
+    """
+
+    def __init__(self, search, agg, plan, scale=10.0, group=None):
+        super().__init__()
+        self.search, self.agg, self.plan, self.scale, self.group = search, agg, plan, scale, group
+
+    def forward(self, q, k, v, flows):
+        k_ext = halo_exchange(k, self.plan, self.group)
+        v_ext = halo_exchange(v, self.plan, self.group)
+        dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
+        sign = -1.0 if self.search.dist_type == "l2" else 1.0
+        weights = th.softmax(sign * self.scale * dists, -1)
+        out = self.agg(v_ext, weights, inds, shard=self.plan.shard)
+        return out, dists, inds

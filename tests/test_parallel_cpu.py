@@ -1,0 +1,83 @@
+"""CPU (gloo, world_size 2 and 3): host logic of the frame-sharded multi-GPU path -- shard plan and the
+differentiable halo exchange -- without any CUDA call."""
+import os
+import socket
+
+import pytest
+import torch as th
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from stnls_b200.parallel import ShardPlan, halo_exchange, needed_frames, shard_frames, time_window
+
+
+def test_time_window_matches_reference_kat():
+    # dev/trange.py:33-41: frames visited from (ti, wt, T)
+    for (ti, wt, T), frames in [((0, 2, 5), [0, 1, 2, 3, 4]), ((1, 2, 5), [1, 2, 3, 4, 0]), ((3, 2, 7), [3, 4, 5, 2, 1]),
+                                ((3, 3, 7), [3, 4, 5, 6, 2, 1, 0]), ((2, 1, 3), [2, 1, 0])]:
+        lo, hi = time_window(ti, T, wt)
+        assert (lo, hi) == (min(frames), max(frames))
+
+
+def test_shard_plan_covers_everything():
+    for T, wt, world in [(40, 2, 8), (64, 3, 8), (10, 2, 4), (7, 3, 2), (5, 2, 1), (9, 1, 4)]:
+        plans = [ShardPlan(T, wt, world, r) for r in range(world)]
+        owned = [f for p in plans for f in range(p.a, p.b)]
+        assert owned == list(range(T))
+        for p in plans:
+            assert p.fa <= p.a and p.b <= p.fb
+            for t in range(p.a, p.b):
+                lo, hi = time_window(t, T, wt)
+                assert p.fa <= lo and hi < p.fb
+            got = sorted(f for _, lo, hi in p.recvs() for f in range(lo, hi)) + list(range(p.a, p.b))
+            assert sorted(got) == list(range(p.fa, p.fb))
+        # every send has a matching receive
+        sends = {(r, d, lo, hi) for r, p in enumerate(plans) for d, lo, hi in p.sends()}
+        recvs = {(s, r, lo, hi) for r, p in enumerate(plans) for s, lo, hi in p.recvs()}
+        assert sends == recvs
+    assert needed_frames(0, 5, 40, 2) == (0, 7)      # clip start: window shifted inward
+    assert needed_frames(35, 40, 40, 2) == (33, 40)  # clip end
+    assert shard_frames(10, 4, 0) == (0, 3) and shard_frames(10, 4, 3) == (8, 10)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, T, wt, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        plan = ShardPlan(T, wt, world, rank)
+        full = th.randn(2, T, 3, 4, 5, generator=th.Generator().manual_seed(0))
+        x = full[:, plan.a:plan.b].clone().requires_grad_(True)
+        ext = halo_exchange(x, plan)
+        ok_fwd = th.equal(ext, full[:, plan.fa:plan.fb])
+        # backward: every rank weights its resident frames with its own coefficients
+        coefs = [th.randn(2, p.fb - p.fa, 3, 4, 5, generator=th.Generator().manual_seed(100 + r))
+                 for r, p in enumerate([ShardPlan(T, wt, world, r) for r in range(world)])]
+        (ext * coefs[rank]).sum().backward()
+        exp = th.zeros(2, plan.b - plan.a, 3, 4, 5)
+        for r in range(world):
+            p = ShardPlan(T, wt, world, r)
+            lo, hi = max(p.fa, plan.a), min(p.fb, plan.b)
+            if lo < hi:
+                exp[:, lo - plan.a:hi - plan.a] += coefs[r][:, lo - p.fa:hi - p.fa]
+        ok_bwd = th.allclose(x.grad, exp, atol=1e-6)
+        ret[rank] = (ok_fwd, ok_bwd)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,T,wt", [(2, 10, 2), (3, 9, 1), (2, 6, 2)])
+def test_halo_exchange_gloo(world, T, wt):
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, _free_port(), T, wt, ret), nprocs=world, join=True)
+    assert len(ret) == world
+    for r in range(world):
+        assert ret[r] == (True, True), (r, ret[r])

@@ -273,7 +273,7 @@ def test_readme_pipeline_backward(cuda, oracle):
     assert_close(vg.grad, to5(gv), 1e-3, 1e-3, "readme grad_v")
     assert_close(qg.grad, to5(g0), 2e-3, 2e-3, "readme grad_q")
     assert_close(kg.grad, to5(g1), 2e-3, 2e-3, "readme grad_k")
-    assert_close(fg.grad, gfl[:, 0], 5e-3, 5e-3, "readme grad_flows")
+    assert_close(fg.grad, gfl, 5e-3, 5e-3, "readme grad_flows")
 
 
 def test_layout_roundtrip_and_errors(cuda):
