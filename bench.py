@@ -1,0 +1,435 @@
+#!/usr/bin/env python
+"""bench.py -- search + weighted-patch-sum forward+backward throughput (BASELINE.json metric).
+
+One *step* = one pass of the hot path over one batch of synthetic video:
+    NonLocalSearch fwd -> softmax -> WeightedPatchSum fwd -> loss -> backward of all three
+(README.md:25-57 of the reference, config C2 of SURVEY.md 8d).  Metric: Gcandidates/s, a candidate
+being one (query, search location) patch comparison = B*HD*T*nH*nW*(2wt+1)*ws*ws per step.
+
+  python bench.py [--gpus N --steps K --warmup W]          product arm (CUDA kernels, C ABI)
+  python bench.py --impl reference ...                    reference arm: the CPU restatement of the
+                                                          reference kernels (oracle/) on the host cores
+N>1 is launched by torchrun, one rank per GPU; frames of ONE clip of T = 5*N frames are sharded over
+ranks (weak scaling) and the +-wt halo frames of k / v travel over NCCL (stnls_b200.parallel).
+
+The JSON line carries `value` (inputs resident in HBM), `e2e` (host buffers in, host buffers out),
+`roofline` (dominant kernel vs measured HBM copy bandwidth), `roofline_fma` (same kernel vs fp32 FMA
+peak at the observed SM clock -- the search forward is FMA-bound), `cpu_baseline`.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch as th  # noqa: E402
+
+WORKLOADS = {
+    # README example on 1 B200 (BASELINE.json configs[1])
+    "c2": dict(B=1, T=5, F=16, H=128, W=128, HD=2, ws=5, wt=2, ps=3, K=10, stride0=1, stride1=0.5,
+               dist_type="l2", self_action="anchor", itype="float", scale=10.0),
+    # RVRT-style (configs[2], C3)
+    "c3": dict(B=2, T=16, F=64, H=256, W=256, HD=4, ws=9, wt=1, ps=1, K=9, stride0=1, stride1=1.0,
+               dist_type="prod", self_action=None, itype="float", scale=10.0),
+    # 1080p slice per rank (configs[3], C4): T frames PER RANK
+    "c4": dict(B=1, T=4, F=64, H=1080, W=1920, HD=4, ws=9, wt=3, ps=3, K=20, stride0=1, stride1=1.0,
+               dist_type="prod", self_action=None, itype="float", scale=10.0),
+}
+
+
+def describe(wl, name, world):
+    c = dict(wl)
+    c["workload"] = {"c2": "README example (BASELINE configs[1]): search+agg fwd+bwd",
+                     "c3": "RVRT-style GDA replacement (BASELINE configs[2])",
+                     "c4": "1080p slice (BASELINE configs[3])"}[name]
+    c["name"] = name
+    c["T_global"] = wl["T"] * world
+    c["sharding"] = "single GPU" if world == 1 else f"T sharded over {world} ranks, NCCL halo exchange of k,v"
+    c["l2_policy"] = "L2 flushed (512 MiB write) before every timed step"
+    return c
+
+
+def candidates_per_step(wl, world=1):
+    nH = (wl["H"] - 1) // wl["stride0"] + 1
+    nW = (wl["W"] - 1) // wl["stride0"] + 1
+    L = (2 * wl["wt"] + 1) * wl["ws"] ** 2
+    return wl["B"] * wl["HD"] * wl["T"] * world * nH * nW * L
+
+
+def make_inputs(wl, rank, world, pin):
+    """Seeded synthetic inputs for the frames this rank owns (SURVEY.md 8d recipe)."""
+    g = th.Generator().manual_seed(1234 + rank)
+    B, T, F, H, W = wl["B"], wl["T"], wl["F"], wl["H"], wl["W"]
+    nH, nW = (H - 1) // wl["stride0"] + 1, (W - 1) // wl["stride0"] + 1
+    W_t = 2 * wl["wt"] + 1
+    q, k, v = [th.randn(B, T, F, H, W, generator=g) for _ in range(3)]
+    fshape = (B, 1, T, W_t - 1, 2, nH, nW)
+    flows = th.rand(fshape, generator=g) / 2 + th.randint(-3, 3, fshape, generator=g) + 0.2
+    if wl["itype"] == "int":
+        flows = flows.round()
+    gout = th.randn(B, wl["HD"], T, F // wl["HD"], H, W, generator=g)
+    ts = [q, k, v, flows, gout]
+    if pin:
+        ts = [t.pin_memory() for t in ts]
+    return ts
+
+
+# ------------------------------------------------------------------------------------------------
+#   algorithmic bytes / flops per launch of each kernel (DESIGN.md "Kernels and rooflines")
+# ------------------------------------------------------------------------------------------------
+
+def algorithmic(wl, Tk):
+    """bytes each kernel must move at minimum (every tensor touched once) and fp32 flops of the
+    search forward, for ONE rank owning wl['T'] query frames and holding Tk key/value frames."""
+    B, HD, T, F, H, W = wl["B"], wl["HD"], wl["T"], wl["F"], wl["H"], wl["W"]
+    Fh = F // HD
+    nH, nW = (H - 1) // wl["stride0"] + 1, (W - 1) // wl["stride0"] + 1
+    W_t, K, ps = 2 * wl["wt"] + 1, wl["K"], wl["ps"]
+    N = B * HD
+    vq, vk = N * T * Fh * H * W * 4, N * Tk * Fh * H * W * 4
+    flows = B * T * (W_t - 1) * 2 * nH * nW * 4
+    dists = N * T * nH * nW * K * 4
+    inds = dists * 3
+    cands = N * T * nH * nW * W_t * wl["ws"] ** 2
+    per_pix = (3 if wl["dist_type"] == "l2" else 2) + (0 if wl["itype"] == "int" else 8)
+    flt = wl["itype"] != "int"
+    return {
+        "search_forward": dict(bytes=vq + vk + flows + dists + inds, flops=cands * ps * ps * Fh * per_pix),
+        # reads q,k,grad_dists,inds(,grad_inds,flows); writes grad_q, grad_k(, grad_flows)
+        "search_backward": dict(bytes=2 * vq + 2 * vk + dists + inds + (inds + 2 * flows if flt else 0)),
+        "wpsum_forward": dict(bytes=vk + dists + inds + vq),          # v, weights, inds -> out
+        # reads grad_out, v, weights, inds; writes grad_v, grad_weights(, grad_flows)
+        "wpsum_backward": dict(bytes=vq + 2 * vk + 2 * dists + inds + (inds if flt else 0)),
+        "pack_cl": dict(bytes=2 * vk), "unpack_cl": dict(bytes=2 * vk),
+        "add_inplace": dict(bytes=0),
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+#   clocks / throttle reasons sampled DURING the timed region (pynvml; nvidia-smi fallback)
+# ------------------------------------------------------------------------------------------------
+
+class ClockSampler:
+    BAD = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown"}
+    NOTE = {0x4: "sw_power_cap"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in list(self.BAD.items()) + list(self.NOTE.items()):
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._loop, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+
+    def summary(self):
+        s = sorted(self.samples)
+        med = s[len(s) // 2] if s else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+#   product arm
+# ------------------------------------------------------------------------------------------------
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def run_product(args):
+    import torch.distributed as dist
+    import stnls_b200
+    from stnls_b200 import ops, parallel
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not th.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product arm has no CPU path)")
+    th.cuda.set_device(local)
+    dev = th.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch N>1 with torchrun)"
+
+    wl = WORKLOADS[args.workload]
+    plan = parallel.ShardPlan(wl["T"] * world, wl["wt"], world, rank)
+    assert plan.b - plan.a == wl["T"]
+    search = stnls_b200.search.NonLocalSearch(wl["ws"], wl["wt"], wl["ps"], wl["K"], nheads=wl["HD"],
+                                              stride0=wl["stride0"], stride1=wl["stride1"],
+                                              dist_type=wl["dist_type"], self_action=wl["self_action"],
+                                              itype=wl["itype"])
+    agg = stnls_b200.agg.WeightedPatchSum(ps=wl["ps"], stride0=wl["stride0"], itype=wl["itype"])
+    model = parallel.ShardedSearchAgg(search, agg, plan, scale=wl["scale"])
+
+    host = make_inputs(wl, rank, world, pin=True)
+    flt = wl["itype"] == "float"
+
+    def step(q, k, v, flows, gout):
+        q.requires_grad_(True); k.requires_grad_(True); v.requires_grad_(True)
+        if flt:
+            flows.requires_grad_(True)
+        out, dists, inds = model(q, k, v, flows)
+        loss = (out * gout).sum()
+        loss.backward()
+        return out, loss
+
+    flush = th.empty(512 << 20, dtype=th.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        th.cuda.synchronize()
+
+    # ---- value: inputs resident in HBM -------------------------------------------------------
+    resident = [t.to(dev) for t in host]
+    for _ in range(args.warmup):
+        step(*[t.detach().clone() for t in resident])
+    barrier()
+    fresh = [[t.detach().clone() for t in resident] for _ in range(args.steps)]
+    evs = []
+    ops.TIMELINE = []
+    launches0 = ops.LAUNCHES
+    barrier()
+    with ClockSampler(local) as clk:
+        for i in range(args.steps):
+            flush.zero_()
+            e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
+            e0.record()
+            step(*fresh[i])
+            e1.record()
+            evs.append((e0, e1))
+        barrier()
+    launches = ops.LAUNCHES - launches0
+    timeline, ops.TIMELINE = ops.TIMELINE, None
+    t_ms = sum(a.elapsed_time(b) for a, b in evs)
+    del fresh
+
+    # ---- e2e: pinned host buffers in, results back to pinned host buffers ----------------------
+    outs_host = None
+    e2e_s = 0.0
+    h2d = sum(t.numel() * t.element_size() for t in host)
+    d2h = 0
+    for i in range(args.warmup + args.steps):
+        flush.zero_()
+        barrier()
+        t0 = time.perf_counter()
+        dev_in = [t.to(dev, non_blocking=True) for t in host]
+        out, loss = step(*dev_in)
+        res = [out.detach(), dev_in[0].grad, dev_in[1].grad, dev_in[2].grad] + ([dev_in[3].grad] if flt else [])
+        if outs_host is None:
+            outs_host = [th.empty(r.shape, dtype=r.dtype).pin_memory() for r in res]
+            d2h = sum(r.numel() * r.element_size() for r in res)
+        for hbuf, r in zip(outs_host, res):
+            hbuf.copy_(r, non_blocking=True)
+        th.cuda.synchronize()
+        if i >= args.warmup:
+            e2e_s += time.perf_counter() - t0
+
+    tt = th.tensor([t_ms, e2e_s * 1e3], dtype=th.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_ms, e2e_ms = float(tt[0]), float(tt[1])
+    return dict(world=world, rank=rank, wl=wl, plan=plan, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
+                launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h)
+
+
+# ------------------------------------------------------------------------------------------------
+#   CPU arm: the C restatement of the reference kernels (oracle/, OpenMP over the host cores)
+# ------------------------------------------------------------------------------------------------
+
+def cpu_pass(wl, crop, threads):
+    """One fwd+bwd pass of the same pipeline on the host.  `crop` = spatial size of the bounded sample."""
+    from oracle import ref
+    os.environ["OMP_NUM_THREADS"] = str(threads)
+    th.set_num_threads(threads)
+    w = dict(wl, H=crop, W=crop)
+    q, k, v, flows, gout = make_inputs(w, 0, 1, pin=False)
+    kw = dict(nheads=w["HD"], stride0=w["stride0"], dist_type=w["dist_type"], itype=w["itype"])
+    flt = w["itype"] == "float"
+    t0 = time.perf_counter()
+    d, i = ref.nls_forward(q, k, flows, w["ws"], w["wt"], w["ps"], w["K"], stride1=w["stride1"],
+                           self_action=w["self_action"], **kw)
+    d.requires_grad_(True)
+    sign = -1.0 if w["dist_type"] == "l2" else 1.0
+    wts = th.softmax(sign * w["scale"] * d, -1)
+    out, counts = ref.gather_add_forward(v, wts.detach(), i, w["ps"], w["stride0"], itype=w["itype"])
+    gv, gw, gf = ref.gather_add_backward(gout, v, wts.detach(), i, counts, w["ps"], w["stride0"], itype=w["itype"])
+    wts.backward(gw)
+    gi = gf if flt else None
+    ref.search_backward(q, k, flows, d.grad, gi, i, w["wt"], w["ps"], flows_grad=flt, **kw)
+    dt = time.perf_counter() - t0
+    return candidates_per_step(w), dt
+
+
+def cpu_sample_size(wl):
+    return min(wl["H"], wl["W"], 64)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    wl = WORKLOADS[args.workload]
+    cores = os.cpu_count() or 1
+    crop = cpu_sample_size(wl)
+    cpu_pass(dict(wl, T=max(2 * wl["wt"] + 1, 2)), 16, cores)  # load + warm the library
+    for _ in range(min(args.warmup, 1)):
+        cpu_pass(wl, crop, cores)
+    steps = max(1, min(args.steps, 3))
+    tot_c, tot_t = 0, 0.0
+    for _ in range(steps):
+        c, t = cpu_pass(wl, crop, cores)
+        tot_c += c
+        tot_t += t
+    val = tot_c / tot_t / 1e9
+    sample = f"{steps} pass(es) of the same pipeline on a {crop}x{crop} crop (T={wl['T']}), OpenMP {cores} threads"
+    line = {"impl": "reference", "metric": "search+agg fwd+bwd throughput", "value": val,
+            "unit": "Gcandidates/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+            "ms_per_step": tot_t / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": describe(wl, args.workload, 1),
+            "cpu_baseline": {"value": val, "unit": "Gcandidates/s", "cores": cores, "kind": "port",
+                             "sample": sample},
+            "e2e": {"value": val, "unit": "Gcandidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "the reference has no CPU path (SURVEY.md 0.4); this is oracle/stnls_oracle.c, a C "
+                    "restatement of its CUDA kernels, pinned against the reference kernels (oracle/_ref)"}
+    print(json.dumps(line), flush=True)
+    return line
+
+
+# ------------------------------------------------------------------------------------------------
+#   assemble the JSON line
+# ------------------------------------------------------------------------------------------------
+
+def kernel_table(timeline, steps):
+    agg = {}
+    for name, e0, e1 in timeline:
+        ms = e0.elapsed_time(e1)
+        a = agg.setdefault(name, [0.0, 0])
+        a[0] += ms
+        a[1] += 1
+    return {n: dict(ms_total=t, launches=c, ms_per_launch=t / c, ms_per_step=t / steps) for n, (t, c) in agg.items()}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="product", choices=["product", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup
+
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    r = run_product(args)
+    if r["rank"] != 0:
+        return
+    wl, world, steps = r["wl"], r["world"], args.steps
+    cands = candidates_per_step(wl, world)
+    ms_per_step = r["t_ms"] / steps
+    value = cands / (ms_per_step * 1e-3) / 1e9
+    e2e_ms = r["e2e_ms"] / steps
+    e2e_val = cands / (e2e_ms * 1e-3) / 1e9
+
+    kt = kernel_table(r["timeline"], steps)
+    plan = r["plan"]
+    alg = algorithmic(wl, plan.fb - plan.fa)
+    main_k = [n for n in kt if n in ("search_forward", "search_backward", "wpsum_forward", "wpsum_backward")]
+    dom = max(main_k, key=lambda n: kt[n]["ms_total"])
+    peak, peak_src = load_peaks()
+    dur_s = kt[dom]["ms_per_launch"] * 1e-3
+    achieved = alg[dom]["bytes"] / dur_s / 1e9
+    roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg[dom]["bytes"], "ms_per_launch": kt[dom]["ms_per_launch"],
+                "share_of_step": kt[dom]["ms_per_step"] / ms_per_step}
+    clocks = r["clocks"]
+    mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965
+    fma_peak = 148 * 128 * 2 * mhz * 1e6 / 1e12
+    fwd = kt.get("search_forward")
+    roofline_fma = None
+    if fwd:
+        af = alg["search_forward"]["flops"] / (fwd["ms_per_launch"] * 1e-3) / 1e12
+        roofline_fma = {"kernel": "search_forward", "bound": "fp32 fma pipe", "achieved": af, "peak": fma_peak,
+                        "unit": "TFLOP/s", "frac": af / fma_peak,
+                        "peak_source": f"148 SM x 128 lanes x 2 x {mhz} MHz (median SM clock under load)",
+                        "algorithmic_flops_per_launch": alg["search_forward"]["flops"]}
+    for n in kt:
+        if n in alg and alg[n]["bytes"]:
+            kt[n]["alg_GBs"] = alg[n]["bytes"] / (kt[n]["ms_per_launch"] * 1e-3) / 1e9
+
+    line = {"metric": "search+agg fwd+bwd throughput", "value": value, "unit": "Gcandidates/s",
+            "n_gpus": world, "steps": steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": describe(wl, args.workload, world),
+            "frames_per_s": wl["B"] * wl["T"] * world / (ms_per_step * 1e-3),
+            "e2e": {"value": e2e_val, "unit": "Gcandidates/s", "h2d_bytes_per_step": r["h2d"],
+                    "d2h_bytes_per_step": r["d2h"], "ms_per_step": e2e_ms,
+                    "what": "pinned host q,k,v,flows,grad_out -> device, fwd+bwd through the Python front end, "
+                            "out + grads of q,k,v,flows back to pinned host; wall clock"},
+            "gpu_launches": r["launches"], "clocks": clocks, "roofline": roofline,
+            "roofline_fma": roofline_fma, "kernels": kt}
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        crop = cpu_sample_size(wl)
+        cpu_pass(dict(wl, T=max(2 * wl["wt"] + 1, 2)), 16, cores)
+        c, t = cpu_pass(wl, crop, cores)
+        line["cpu_baseline"] = {"value": c / t / 1e9, "unit": "Gcandidates/s", "cores": cores, "kind": "port",
+                                "sample": f"1 pass of the same pipeline on a {crop}x{crop} crop (T={wl['T']}), "
+                                          f"oracle/stnls_oracle.c with OpenMP, {t:.1f} s"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -11,6 +11,25 @@ from ._C import AggOpts, Geom, SearchOpts
 
 MAX_FUSED_K = 32
 
+# launch accounting: every C-ABI call below launches exactly one of our kernels.  `LAUNCHES` counts
+# them; when `TIMELINE` is a list, each launch is bracketed by CUDA events on the launching stream
+# (bench.py reads them for the per-kernel roofline).
+LAUNCHES = 0
+TIMELINE = None
+
+
+def _launch(name, fn, *args):
+    global LAUNCHES
+    LAUNCHES += 1
+    if TIMELINE is None:
+        _C.check(fn(*args))
+        return
+    e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
+    e0.record()
+    _C.check(fn(*args))
+    e1.record()
+    TIMELINE.append((name, e0, e1))
+
 
 def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
@@ -60,8 +79,8 @@ def pack_cl(vid, nheads, t0=0, Tloc=None, counts=None):
     Fp = padded_channels(F)
     out = th.empty((B * HD, Tloc, H, W, Fp), device=vid.device, dtype=th.float32)
     ch, cw = (None, None) if counts is None else counts
-    _C.check(_C.lib().stnls_pack_cl(_ptr(out), _ptr(vid), B, HD, t0, Tloc, F, Fp, H, W,
-                                    sB, sHD, sT, sC, _ptr(ch), _ptr(cw), _stream()))
+    _launch("pack_cl", _C.lib().stnls_pack_cl, _ptr(out), _ptr(vid), B, HD, t0, Tloc, F, Fp, H, W,
+                                    sB, sHD, sT, sC, _ptr(ch), _ptr(cw), _stream())
     return out
 
 
@@ -73,8 +92,8 @@ def unpack_cl(cl, shape, nheads, t0=0, out=None, accumulate=False):
     _, (B, HD, T, F, H, W), (sB, sHD, sT, sC) = _planar_strides(out, nheads)
     Tloc, Fp = cl.shape[1], cl.shape[4]
     assert cl.shape[0] == B * HD and cl.shape[2] == H and cl.shape[3] == W and cl.is_contiguous()
-    _C.check(_C.lib().stnls_unpack_cl(_ptr(out), _ptr(cl), B, HD, t0, Tloc, F, Fp, H, W,
-                                      sB, sHD, sT, sC, int(accumulate), _stream()))
+    _launch("unpack_cl", _C.lib().stnls_unpack_cl, _ptr(out), _ptr(cl), B, HD, t0, Tloc, F, Fp, H, W,
+                                      sB, sHD, sT, sC, int(accumulate), _stream())
     return out
 
 
@@ -101,9 +120,9 @@ def search_forward(q_cl, k_cl, flows, geom, opts):
         kselect = th.empty(dists.shape, device=dev, dtype=th.int32)
         reflect = th.zeros(tuple(flows.shape[:-1]) + (2,), device=dev, dtype=th.uint8)
     assert flows.is_contiguous() and flows.dtype == itype
-    _C.check(_C.lib().stnls_search_forward(_ptr(q_cl), _ptr(k_cl), _ptr(flows), _ptr(dists), _ptr(inds),
+    _launch("search_forward", _C.lib().stnls_search_forward, _ptr(q_cl), _ptr(k_cl), _ptr(flows), _ptr(dists), _ptr(inds),
                                            _ptr(kselect), _ptr(reflect), ctypes.byref(g), ctypes.byref(o),
-                                           _stream()))
+                                           _stream())
     return dists, inds, kselect, reflect
 
 
@@ -123,11 +142,11 @@ def search_backward(q_cl, k_cl, flows, grad_dists, grad_inds, inds, kselect, ref
         grad_inds = grad_inds.contiguous().float()
         if reflect is not None:
             reflect = reflect.to(th.uint8).contiguous()
-    _C.check(_C.lib().stnls_search_backward(_ptr(gq), _ptr(gk), _ptr(gflows), _ptr(q_cl), _ptr(k_cl),
+    _launch("search_backward", _C.lib().stnls_search_backward, _ptr(gq), _ptr(gk), _ptr(gflows), _ptr(q_cl), _ptr(k_cl),
                                             _ptr(flows if flows_grad else None), _ptr(grad_dists),
                                             _ptr(grad_inds if flows_grad else None), _ptr(inds),
                                             _ptr(kselect), _ptr(reflect), K,
-                                            ctypes.byref(g), ctypes.byref(o), _stream()))
+                                            ctypes.byref(g), ctypes.byref(o), _stream())
     return gq, gk, gflows
 
 
@@ -148,9 +167,9 @@ def wpsum_forward(v_cl, weights, flows, counts, geom, opts):
     _need_cuda(v_cl, weights, flows)
     g = geom
     out = th.empty((g.B * g.HD, g.Tq, g.kH, g.kW, g.Fp), device=v_cl.device, dtype=th.float32)
-    _C.check(_C.lib().stnls_wpsum_forward(_ptr(out), _ptr(v_cl), _ptr(weights), _ptr(flows),
+    _launch("wpsum_forward", _C.lib().stnls_wpsum_forward, _ptr(out), _ptr(v_cl), _ptr(weights), _ptr(flows),
                                           _ptr(counts[0]), _ptr(counts[1]),
-                                          ctypes.byref(g), ctypes.byref(opts), _stream()))
+                                          ctypes.byref(g), ctypes.byref(opts), _stream())
     return out
 
 
@@ -159,13 +178,13 @@ def wpsum_backward(gout_cl, v_cl, weights, flows, geom, opts):
     gv = th.zeros_like(v_cl)
     gw = th.zeros_like(weights)
     gf = None if opts.itype_int else th.zeros(flows.shape, device=flows.device, dtype=th.float32)
-    _C.check(_C.lib().stnls_wpsum_backward(_ptr(gv), _ptr(gw), _ptr(gf), _ptr(gout_cl), _ptr(v_cl),
+    _launch("wpsum_backward", _C.lib().stnls_wpsum_backward, _ptr(gv), _ptr(gw), _ptr(gf), _ptr(gout_cl), _ptr(v_cl),
                                            _ptr(weights), _ptr(flows),
-                                           ctypes.byref(geom), ctypes.byref(opts), _stream()))
+                                           ctypes.byref(geom), ctypes.byref(opts), _stream())
     return gv, gw, gf
 
 
 def add_inplace(dst, src):
     assert dst.is_contiguous() and src.is_contiguous() and dst.numel() == src.numel()
-    _C.check(_C.lib().stnls_add_inplace(_ptr(dst), _ptr(src), dst.numel(), _stream()))
+    _launch("add_inplace", _C.lib().stnls_add_inplace, _ptr(dst), _ptr(src), dst.numel(), _stream())
     return dst
