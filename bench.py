@@ -120,6 +120,7 @@ class ClockSampler:
 
     def __init__(self, index):
         self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.period = float(os.environ.get("BENCH_CLOCK_PERIOD", "0.02"))
         self._stop = threading.Event()
         self._thr = None
         try:
@@ -145,7 +146,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(self.period)
 
     def __enter__(self):
         if self.nv is not None:

@@ -1,0 +1,30 @@
+// Lattice-table forward search: host-visible configuration + launcher declarations.
+// The kernel itself is in search_fwd_tab_kernel.cuh and is instantiated in four translation units
+// (search_fwd_tab_{nls,ref}_{int,float}.cu) so the template variants compile in parallel.
+#pragma once
+#include "search_fwd_common.cuh"
+
+namespace stnls_fwd {
+
+struct TabCfg {
+  int n1, n2;     // lattice steps of one candidate step / one patch-pixel step
+  float u;        // lattice unit
+  int M, Mp;      // lattice points per axis (<= 32), row pitch of T (float4 units)
+  int PS4, GS4;   // plane (channel quad) stride and group stride of T, float4 units
+  int nb;         // groups per batch
+  int Q4, q4sh;   // channel quads; log2(Q4) or -1
+  int ax_rounds;  // 1: both axes of a group in one 32-lane round (M <= 16), 2: one round per axis
+  unsigned rpat;  // bits n2*p, p < ps: lattice rows/cols one patch touches relative to its first
+  int dec_f4;     // float4s of the per-CTA item decode table
+  int q_off, ax_off, msk_off, key_off, warp_f4;  // per-warp smem carve, float4 units
+  int wpb;        // warps per block
+  float inv_G, inv_wsz, inv_Q4, inv_M;
+};
+
+// one per translation unit; each picks dist_type / ps / channel-quad template variants at run time
+int launch_tab_nls_int(const FwdParams& P, const TabCfg& C, cudaStream_t st);
+int launch_tab_nls_float(const FwdParams& P, const TabCfg& C, cudaStream_t st);
+int launch_tab_ref_int(const FwdParams& P, const TabCfg& C, cudaStream_t st);
+int launch_tab_ref_float(const FwdParams& P, const TabCfg& C, cudaStream_t st);
+
+}  // namespace stnls_fwd

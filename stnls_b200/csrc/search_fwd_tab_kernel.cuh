@@ -1,0 +1,422 @@
+// "Lattice table" forward search kernel.
+//
+// All patch pixels of all candidates of one (query, group) -- group = frame slot of the NLS window or
+// input offset of a refinement -- lie on a lattice  pos(m) = base + u*m  per axis (u = 1 for integer
+// stride1; 1/2, 1/4 for stride1 = 0.5, 0.25).  One warp owns one query and, per batch of groups:
+//   1. axis tables   per (group, axis, m): reflected position -> tap offsets, bilinear weights, validity
+//   2. lattice table T[group][channel quad][mh][mw] (shared memory): the key value at every lattice
+//      point, bilinear-interpolated ONCE (the reference re-interpolates it for each of the ~ps*ps
+//      candidates whose patches cover it); global loads coalesced over channel quads
+//   3. candidates    lane = candidate; ps*ps*F_head FMAs reading T and the query patch from shared
+//      memory, accumulated in the reference's order (pi -> pj -> channel) so the int path stays
+//      bit-identical to the reference kernels
+//   4. keys of all L candidates stay in shared memory; the K best are then picked by K rounds of
+//      redux.sync min over the warp (ties -> lower candidate index).
+// Reference semantics: SURVEY.md appendix A; lib/csrc/search/nls_{int,bilin2d}.cu,
+// lib/csrc/shared_kernel.cu:49-60,248-287,738-771, lib/csrc/nn/anchor_self_kernel.cu:24-116,547-650,
+// lib/stnls/nn/topk.py:65-123.
+#pragma once
+#include "search_fwd_tab.cuh"
+
+namespace stnls_fwd {
+
+__device__ __forceinline__ int fdiv(int x, float inv) { return __float2int_rz(((float)x + 0.5f) * inv); }
+
+// order-preserving float -> uint map (smaller float <=> smaller uint); 0xffffffff is reserved for "taken"
+__device__ __forceinline__ unsigned f2ord(float f) {
+  unsigned b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__device__ __forceinline__ void fma4(float4& v, float w, const float4 t) {
+  v.x = fmaf(w, t.x, v.x); v.y = fmaf(w, t.y, v.y); v.z = fmaf(w, t.z, v.z); v.w = fmaf(w, t.w, v.w);
+}
+
+// key value at one lattice point: plain read (int) or 4-tap bilinear, taps outside the frame dropped
+// (shared_kernel.cu:738-771; tap order (0,0),(0,1),(1,0),(1,1) and weight gh*gw as in the reference)
+template <bool INT>
+__device__ __forceinline__ float4 lattice_value(const float* kc, const float4 eh, const float4 ew) {
+  const int oh0 = __float_as_int(eh.x), ow0 = __float_as_int(ew.x);
+  if (INT) return ldg4(kc + (unsigned)(oh0 + ow0));
+  const int oh1 = __float_as_int(eh.y), ow1 = __float_as_int(ew.y);
+  float4 v = f4zero();
+  if ((oh0 | ow0) >= 0) fma4(v, eh.z * ew.z, ldg4(kc + (unsigned)(oh0 + ow0)));
+  if ((oh0 | ow1) >= 0) fma4(v, eh.z * ew.w, ldg4(kc + (unsigned)(oh0 + ow1)));
+  if ((oh1 | ow0) >= 0) fma4(v, eh.w * ew.z, ldg4(kc + (unsigned)(oh1 + ow0)));
+  if ((oh1 | ow1) >= 0) fma4(v, eh.w * ew.w, ldg4(kc + (unsigned)(oh1 + ow1)));
+  return v;
+}
+
+// PS: patch size (0 = run time); Q4T: channel quads (0 = run time)
+template <bool INT, int DIST, bool REFINE, int PS, int Q4T>
+__global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_constant__ FwdParams P,
+                                                                const __grid_constant__ TabCfg C) {
+  typedef typename CT<INT>::type CC;
+  extern __shared__ float4 smem4[];
+  int* const smi = reinterpret_cast<int*>(smem4);
+  unsigned* const smu = reinterpret_cast<unsigned*>(smem4);
+  const unsigned short* const dec = reinterpret_cast<const unsigned short*>(smem4);
+  const stnls_geom& g = P.g;
+  const stnls_search_opts& o = P.o;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int M = C.M;
+  const int Q4 = (Q4T > 0) ? Q4T : C.Q4;
+  const int ps = (PS > 0) ? PS : o.ps, ps2 = ps * ps;
+
+  // per-CTA decode table of the lattice points: x -> (mh << 8) | mw
+  for (int x = threadIdx.x; x < M * M; x += blockDim.x) {
+    int mh = fdiv(x, C.inv_M);
+    reinterpret_cast<unsigned short*>(smem4)[x] = (unsigned short)((mh << 8) | (x - mh * M));
+  }
+  __syncthreads();
+
+  const int64_t wq = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
+  if (wq >= P.nquery) return;
+  // per-warp smem carve (float4 indices into smem4)
+  const int Tb = C.dec_f4 + warp * C.warp_f4;
+  const int qb = Tb + C.q_off;
+  const int axb = Tb + C.ax_off;              // AxEntry[nb][2][M], one float4 each: (o0, o1, w0, w1)
+  const int mskb = (Tb + C.msk_off) * 4;      // uint index: [nb][2] validity masks, then [nb] frame slot
+  const int gfrb = mskb + 2 * C.nb;
+  const int keyb = (Tb + C.key_off) * 4;      // uint index: [L] ordered keys
+
+  // -- decode query (shared_kernel.cu:76-98) --
+  QueryCtx c;
+  int64_t r = wq;
+  c.nw = (int)(r % g.nW); r /= g.nW;
+  c.nh = (int)(r % g.nH); r /= g.nH;
+  c.tl = (int)(r % g.Tq); r /= g.Tq;
+  c.n = (int)r;
+  c.hd = c.n % g.HD;
+  c.b = c.n / g.HD;
+  c.t = c.tl + g.tq0;
+  c.ah = (c.nh * o.stride0) % g.kH;
+  c.aw = (c.nw * o.stride0) % g.kW;
+  if (INT) { c.rh = (c.nh * o.strideQ) % g.qH; c.rw = (c.nw * o.strideQ) % g.qW; }
+  else { c.rh = c.ah; c.rw = c.aw; }
+  c.t_max = time_tmax(c.t, g.T, o.wt);
+
+  const float* qf = P.q + ((int64_t)c.n * g.Tq + c.tl) * g.qH * g.qW * g.Fp;
+  const float* kbase = P.k + (int64_t)c.n * g.Tk * g.kH * g.kW * g.Fp;
+  const int64_t kfs = (int64_t)g.kH * g.kW * g.Fp;
+  const float invalid = (DIST == 0) ? -INFINITY : INFINITY;
+  const bool anchored = o.anchor_self != 0;
+  const bool keep_all = o.K <= 0;
+  const int64_t obase = wq * P.Kout;
+  CC* inds_out = reinterpret_cast<CC*>(P.inds);
+
+  // -- query patch -> smem (once); validity mask of its pixels --
+  unsigned qmask;
+  {
+    bool ok = false;
+    int qo = 0;
+    if (lane < ps2) {
+      int pi = lane / ps, pj = lane - pi * ps;
+      int r1 = c.rh + o.off_Hq + o.dilation * (pi + o.patch_offset);
+      int r2 = c.rw + o.off_Wq + o.dilation * (pj + o.patch_offset);
+      if (o.reflect_bounds) { r1 = bnd(r1, g.qH); r2 = bnd(r2, g.qW); }
+      ok = inb(r1, g.qH) && inb(r2, g.qW);
+      qo = (r1 * g.qW + r2) * g.Fp;
+    }
+    qmask = __ballot_sync(FULL_MASK, ok);
+    for (int base = 0; base < ps2 * Q4; base += 32) {
+      int it = base + lane;
+      int p = (Q4T > 0 || C.q4sh >= 0) ? (it >> C.q4sh) : fdiv(it, C.inv_Q4);
+      int c4 = it - p * Q4;
+      int po = __shfl_sync(FULL_MASK, qo, p & 31);
+      if (it < ps2 * Q4 && ((qmask >> p) & 1)) smem4[qb + it] = ldg4(qf + po + c4 * 4);
+    }
+  }
+  const bool qfull = qmask == ((ps2 >= 32) ? 0xffffffffu : ((1u << ps2) - 1u));
+
+  // -- pass 1 (NLS anchor): candidate whose offset is (0,0,0) / nearest to it (anchor_self_kernel.cu:62-89)
+  int a_nls = 0;
+  if (anchored && !REFINE) {
+    float bkey = INFINITY;
+    int bpos = 0x7fffffff;
+    const CC zero[3] = {(CC)0, (CC)0, (CC)0};
+    const int nchunks = (P.nG + 31) / 32;
+    for (int ch = 0; ch < nchunks; ch++) {
+      int gi = ch * 32 + lane;
+      Group<CC> mine = group_params<INT, REFINE>(P, c, min(gi, P.nG - 1));
+      int pend = min(P.L, (ch + 1) * 32 * P.G);
+      for (int base = ch * 32 * P.G; base < pend; base += 32) {
+        int pos = min(base + lane, pend - 1);
+        int gq = fdiv(pos, C.inv_G);
+        Group<CC> gp = shfl_group(mine, gq - ch * 32);
+        int s = pos - gq * P.G;
+        int wi = fdiv(s, C.inv_wsz), wj = s - wi * P.wsz;
+        CC ind[3];
+        ind[0] = (CC)gp.t - (CC)c.t;
+        if (INT) {
+          ind[1] = (CC)((int)gp.ah + (int)o.stride1 * (wi - (int)gp.offh) - c.ah);
+          ind[2] = (CC)((int)gp.aw + (int)o.stride1 * (wj - (int)gp.offw) - c.aw);
+        } else {
+          ind[1] = (CC)(fmaf(o.stride1, (float)wi - (float)gp.offh, (float)gp.ah) - (float)c.ah);
+          ind[2] = (CC)(fmaf(o.stride1, (float)wj - (float)gp.offw, (float)gp.aw) - (float)c.aw);
+        }
+        float key = anchor_key(ind, zero);
+        if (base + lane < pend && (key < bkey || (key == bkey && pos < bpos)) && key < INFINITY) { bkey = key; bpos = pos; }
+      }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      float ok = __shfl_xor_sync(FULL_MASK, bkey, off);
+      int op = __shfl_xor_sync(FULL_MASK, bpos, off);
+      if (ok < bkey || (ok == bkey && op < bpos)) { bkey = ok; bpos = op; }
+    }
+    a_nls = (bpos == 0x7fffffff) ? 0 : bpos;
+  }
+
+  // -- pass 2: per batch of groups: axis tables -> lattice table -> candidate distances --
+  const CC s1c = INT ? (CC)(int)o.stride1 : (CC)o.stride1;
+  const int rowsc = g.kW * g.Fp;  // floats per key row
+  for (int g0 = 0; g0 < P.nG; g0 += C.nb) {
+    const int nbg = min(C.nb, P.nG - g0);
+    Group<CC> mine = group_params<INT, REFINE>(P, c, g0 + min(lane, nbg - 1));
+    int my_ag = 0;
+    if (REFINE && anchored) my_ag = refine_group_anchor<CC>(P, c, mine, g0 + min(lane, nbg - 1));
+    if (lane < nbg) smi[gfrb + lane] = (mine.ok && inb(mine.t, g.T)) ? (mine.t - g.tk0) : -1;
+    // 1. axis tables: one 32-lane round per group (both axes, M <= 16) or per (group, axis)
+    for (int rd = 0; rd < nbg * C.ax_rounds; rd++) {
+      int gl, axis, m;
+      if (C.ax_rounds == 1) { gl = rd; axis = lane >> 4; m = lane & 15; }
+      else { gl = rd >> 1; axis = rd & 1; m = lane; }
+      Group<CC> gp = shfl_group(mine, gl);
+      const int lim = axis ? g.kW : g.kH;
+      const int sc = axis ? g.Fp : rowsc;
+      const CC a = axis ? gp.aw : gp.ah, off = axis ? gp.offw : gp.offh;
+      bool pv = false;
+      int o0 = -1, o1 = -1;
+      float w0 = 0.f, w1 = 0.f;
+      if (m < M) {
+        if (INT) {
+          int p = (int)a - (int)s1c * (int)off + o.dilation * o.patch_offset + m;
+          if (o.reflect_bounds) p = bnd(p, lim);
+          pv = inb(p, lim);
+          o0 = pv ? p * sc : -1;
+        } else {
+          float basep = fmaf(-(float)s1c, (float)off, (float)a) + (float)(o.dilation * o.patch_offset);
+          float p = fmaf(C.u, (float)m, basep);
+          if (o.reflect_bounds) p = bnd(p, lim);
+          pv = inb(p, lim);
+          int t0 = __float2int_rz(p), t1 = __float2int_rz(p + 1);
+          w0 = fmaxf(0.f, 1 - fabsf(t0 - p));
+          w1 = fmaxf(0.f, 1 - fabsf(t1 - p));
+          o0 = inb(t0, lim) ? t0 * sc : -1;
+          o1 = inb(t1, lim) ? t1 * sc : -1;
+        }
+        smem4[axb + (gl * 2 + axis) * M + m] = make_float4(__int_as_float(o0), __int_as_float(o1), w0, w1);
+      }
+      unsigned bal = __ballot_sync(FULL_MASK, pv);
+      if (lane == 0) {
+        if (C.ax_rounds == 1) { smu[mskb + gl * 2] = bal & 0xffffu; smu[mskb + gl * 2 + 1] = bal >> 16; }
+        else smu[mskb + gl * 2 + axis] = bal;
+      }
+    }
+    __syncwarp();
+    // 2. lattice table: item = (mh, mw, channel quad), quads fastest so a warp reads whole pixels
+    const int MM = M * M;
+    for (int gl = 0; gl < nbg; gl++) {
+      const int fr = smi[gfrb + gl];
+      if (fr < 0) continue;
+      const unsigned mh_ok = smu[mskb + gl * 2], mw_ok = smu[mskb + gl * 2 + 1];
+      const int Ah = axb + (gl * 2) * M, Aw = Ah + M;
+      const int Tg = Tb + gl * C.GS4;
+      const float* kf = kbase + (int64_t)fr * kfs;
+      if (Q4T > 0) {  // 32 % Q4T == 0: the channel quad of a lane never changes
+        const int c4 = lane & (Q4T - 1);
+        const float* kc = kf + c4 * 4;
+        const int Tgc = Tg + c4 * C.PS4;
+        for (int x = lane / Q4T; x < MM; x += 32 / Q4T) {
+          const unsigned d = dec[x];
+          const int mh = d >> 8, mw = d & 255;
+          if (!(((mh_ok >> mh) & (mw_ok >> mw)) & 1)) continue;
+          smem4[Tgc + mh * C.Mp + mw] = lattice_value<INT>(kc, smem4[Ah + mh], smem4[Aw + mw]);
+        }
+      } else {
+        for (int it = lane; it < MM * Q4; it += 32) {
+          int x, c4;
+          if (C.q4sh >= 0) { x = it >> C.q4sh; c4 = it & (Q4 - 1); }
+          else { x = fdiv(it, C.inv_Q4); c4 = it - x * Q4; }
+          const unsigned d = dec[x];
+          const int mh = d >> 8, mw = d & 255;
+          if (!(((mh_ok >> mh) & (mw_ok >> mw)) & 1)) continue;
+          smem4[Tg + c4 * C.PS4 + mh * C.Mp + mw] = lattice_value<INT>(kf + c4 * 4, smem4[Ah + mh], smem4[Aw + mw]);
+        }
+      }
+    }
+    __syncwarp();
+    // 3. candidates of this batch: lane = candidate
+    const int nC = nbg * P.G;
+    for (int base = 0; base < nC; base += 32) {
+      const bool active = base + lane < nC;
+      const int posb = min(base + lane, nC - 1);
+      const int gl = (C.nb == 1) ? 0 : fdiv(posb, C.inv_G);
+      const int s = posb - gl * P.G;
+      const int gq = g0 + gl;
+      const int pos = gq * P.G + s;
+      const int wi = fdiv(s, C.inv_wsz), wj = s - wi * P.wsz;
+      Group<CC> gp = shfl_group(mine, gl);
+      const int ag = (REFINE && anchored) ? __shfl_sync(FULL_MASK, my_ag, gl) : 0;
+      CC chh, cww;
+      if (INT) {
+        chh = (CC)((int)gp.ah + (int)s1c * (wi - (int)gp.offh));
+        cww = (CC)((int)gp.aw + (int)s1c * (wj - (int)gp.offw));
+      } else {
+        chh = (CC)fmaf((float)s1c, (float)wi - (float)gp.offh, (float)gp.ah);
+        cww = (CC)fmaf((float)s1c, (float)wj - (float)gp.offw, (float)gp.aw);
+      }
+      const bool cvalid = active && gp.ok && inb(gp.t, g.T) && inb(chh, g.kH) && inb(cww, g.kW);
+      const int mh0 = C.n1 * wi, mw0 = C.n1 * wj;
+      const unsigned hm = smu[mskb + gl * 2] >> mh0, wm = smu[mskb + gl * 2 + 1] >> mw0;
+      const int Tc = Tb + gl * C.GS4 + mh0 * C.Mp + mw0;
+      const bool allpix = qfull && ((hm & C.rpat) == C.rpat) && ((wm & C.rpat) == C.rpat);
+      float d = invalid;
+      if (__all_sync(FULL_MASK, allpix || !cvalid)) {
+        // every pixel pair of every live candidate is valid: straight-line code
+        if (cvalid) {
+          float dist = 0.f;
+#pragma unroll
+          for (int pi = 0; pi < ps; pi++) {
+#pragma unroll
+            for (int pj = 0; pj < ps; pj++) {
+              const int tp = Tc + C.n2 * (pi * C.Mp + pj);
+              const int qp = qb + (pi * ps + pj) * Q4;
+#pragma unroll
+              for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, smem4[qp + c4], smem4[tp + c4 * C.PS4]);
+            }
+          }
+          d = dist;
+        }
+      } else if (cvalid) {
+        float dist = 0.f;
+        for (int pi = 0; pi < ps; pi++) {
+          if (!((hm >> (C.n2 * pi)) & 1)) continue;
+          for (int pj = 0; pj < ps; pj++) {
+            if (!(((wm >> (C.n2 * pj)) & (qmask >> (pi * ps + pj))) & 1)) continue;
+            const int tp = Tc + C.n2 * (pi * C.Mp + pj);
+            const int qp = qb + (pi * ps + pj) * Q4;
+            for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, smem4[qp + c4], smem4[tp + c4 * C.PS4]);
+          }
+        }
+        d = dist;
+      }
+      // position after the anchor swap (an involution; anchor_self_kernel.cu:101-113)
+      int eff = pos;
+      if (anchored) {
+        if (REFINE) { if (s == 0) eff = gq * P.G + ag; else if (s == ag) eff = gq * P.G; }
+        else { if (pos == 0) eff = a_nls; else if (pos == a_nls) eff = 0; }
+      }
+      if (keep_all || (anchored && eff == 0)) {
+        if (active) {
+          const bool to_slot0 = anchored && (REFINE ? (eff % P.G == 0 && ag != 0) : (eff == 0 && a_nls != 0));
+          int64_t oi = obase + (keep_all ? eff : 0);
+          CC ind[3];
+          if (to_slot0) {
+            if (REFINE) refine_loc<CC>(P, c, eff / P.G, ind);
+            else ind[0] = ind[1] = ind[2] = (CC)0;
+          } else cand_inds<CC>(P, c, gp, s, ind);
+          P.dists[oi] = d;
+          inds_out[oi * 3] = ind[0]; inds_out[oi * 3 + 1] = ind[1]; inds_out[oi * 3 + 2] = ind[2];
+          if (P.kselect) P.kselect[oi] = gp.ok ? gq : 1;
+        }
+        if (keep_all) continue;
+      }
+      if (active && !(anchored && eff == 0))
+        smu[keyb + eff] = min(f2ord(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu);
+    }
+    __syncwarp();
+  }
+  if (keep_all) return;
+
+  // -- 4. selection: K rounds of warp-wide min over the keys (ties -> lower candidate index) --
+  const int Klist = anchored ? P.Kout - 1 : P.Kout;
+  const int start = lane + ((anchored && lane == 0) ? 32 : 0);
+  unsigned bk = 0xffffffffu;
+  int bi = 0x7fffffff;
+  for (int i = start; i < P.L; i += 32) {
+    unsigned kv = smu[keyb + i];
+    if (kv < bk) { bk = kv; bi = i; }
+  }
+  unsigned mykey = 0xffffffffu;
+  int mypos = 0x7fffffff;
+  for (int kk = 0; kk < Klist; kk++) {
+    const unsigned m = __reduce_min_sync(FULL_MASK, bk);
+    if (m == 0xffffffffu) break;
+    const int widx = (int)__reduce_min_sync(FULL_MASK, (bk == m) ? (unsigned)bi : 0x7fffffffu);
+    if (lane == kk) { mykey = m; mypos = widx; }
+    if (bi == widx) {
+      smu[keyb + bi] = 0xffffffffu;
+      bk = 0xffffffffu;
+      bi = 0x7fffffff;
+      for (int i = start; i < P.L; i += 32) {
+        unsigned kv = smu[keyb + i];
+        if (kv < bk) { bk = kv; bi = i; }
+      }
+    }
+  }
+
+  // -- write the list: recompute the offsets of the kept candidates --
+  if (lane < Klist && mypos != 0x7fffffff) {
+    int eff = mypos;
+    int64_t oi = obase + (anchored ? lane + 1 : lane);
+    int gq = eff / P.G, s = eff - gq * P.G;
+    Group<CC> gp = group_params<INT, REFINE>(P, c, gq);
+    CC ind[3];
+    bool done = false;
+    if (anchored) {
+      if (REFINE) {
+        int ag = refine_group_anchor<CC>(P, c, gp, gq);
+        if (s == 0 && ag != 0) { refine_loc<CC>(P, c, gq, ind); done = true; }
+        else if (s == ag) s = 0;
+      } else {
+        if (eff == a_nls) { gq = 0; s = 0; gp = group_params<INT, REFINE>(P, c, 0); }
+      }
+    }
+    if (!done) cand_inds<CC>(P, c, gp, s, ind);
+    const float kf_ = ord2f(mykey);
+    P.dists[oi] = (DIST == 0) ? -kf_ : kf_;
+    inds_out[oi * 3] = ind[0]; inds_out[oi * 3 + 1] = ind[1]; inds_out[oi * 3 + 2] = ind[2];
+    if (P.kselect) P.kselect[oi] = gp.ok ? gq : 1;
+  }
+}
+
+template <bool INT, int DIST, bool REFINE, int PS, int Q4T>
+int launch_tab_one(const FwdParams& P, const TabCfg& C, cudaStream_t st) {
+  size_t smem = ((size_t)C.dec_f4 + (size_t)C.wpb * C.warp_f4) * 16;
+  auto kern = search_fwd_tab_kernel<INT, DIST, REFINE, PS, Q4T>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return -1;
+  }
+  int64_t blocks = (P.nquery + C.wpb - 1) / C.wpb;
+  kern<<<(unsigned)blocks, C.wpb * 32, smem, st>>>(P, C);
+  return 0;
+}
+
+template <bool INT, int DIST, bool REFINE, int PS>
+int launch_tab_q4(const FwdParams& P, const TabCfg& C, cudaStream_t st) {
+  if (C.Q4 == 2) return launch_tab_one<INT, DIST, REFINE, PS, 2>(P, C, st);
+  if (C.Q4 == 4) return launch_tab_one<INT, DIST, REFINE, PS, 4>(P, C, st);
+  return launch_tab_one<INT, DIST, REFINE, PS, 0>(P, C, st);
+}
+
+template <bool INT, bool REFINE>
+int launch_tab_all(const FwdParams& P, const TabCfg& C, cudaStream_t st) {
+  const int ps = P.o.ps;
+  if (P.o.dist_type == 0) {
+    if (ps == 1) return launch_tab_q4<INT, 0, REFINE, 1>(P, C, st);
+    if (ps == 3) return launch_tab_q4<INT, 0, REFINE, 3>(P, C, st);
+    return launch_tab_q4<INT, 0, REFINE, 0>(P, C, st);
+  }
+  if (ps == 1) return launch_tab_q4<INT, 1, REFINE, 1>(P, C, st);
+  if (ps == 3) return launch_tab_q4<INT, 1, REFINE, 3>(P, C, st);
+  return launch_tab_q4<INT, 1, REFINE, 0>(P, C, st);
+}
+
+}  // namespace stnls_fwd
