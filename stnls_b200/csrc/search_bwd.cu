@@ -6,8 +6,16 @@
 //   nls_bwd_vid_kernel / nls_bwd_vidflows_kernel lib/csrc/search/non_local_search_bilin2d_kernel.cu:285-371,464-598
 //   refinement_vidflows_backward_kernel        lib/csrc/search/refinement_bilin2d_kernel.cu:359-491
 #include "common.cuh"
+#include <cstdlib>
 
 namespace {
+
+__device__ __forceinline__ float dot4(const float4 a, const float4 b) {
+  return fmaf(a.w, b.w, fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)));
+}
+__device__ __forceinline__ void fma4(float4& y, float a, const float4 x) {
+  y.x = fmaf(a, x.x, y.x); y.y = fmaf(a, x.y, y.y); y.z = fmaf(a, x.z, y.z); y.w = fmaf(a, x.w, y.w);
+}
 
 struct BwdParams {
   float* gq;
@@ -23,13 +31,14 @@ struct BwdParams {
   const uint8_t* reflect;
   stnls_geom g;
   stnls_search_opts o;
-  int K, mode, nquad, W_t;
+  int K, mode, nquad, W_t, fast3;
   int64_t nthreads;
 };
 
 // MODE 0: int ; 1: bilinear ; 2: bilinear + flow grads (NLS layout) ; 3: same, refine layout
-template <int MODE, int DIST, int PS>
-__global__ void __launch_bounds__(128) search_bwd_kernel(const __grid_constant__ BwdParams P) {
+// PS > 0: compile-time patch size (grad_q of the patch is kept in registers over the K neighbours)
+template <int MODE, int DIST, int PS, bool FAST>
+__global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __grid_constant__ BwdParams P) {
   const stnls_geom& g = P.g;
   const stnls_search_opts& o = P.o;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -58,10 +67,10 @@ __global__ void __launch_bounds__(128) search_bwd_kernel(const __grid_constant__
 #pragma unroll
   for (int i = 0; i < ((PS > 0) ? PS * PS : 1); i++) acc[i] = f4zero();
 
-  for (int ki = 0; ki < P.K; ki++) {
-    const int64_t oi = wq * P.K + ki;
-    const float weight = P.gd[oi];
-    if (MODE == 0) {
+  if (MODE == 0) {  // nls_int.cu:88-167
+    for (int ki = 0; ki < P.K; ki++) {
+      const int64_t oi = wq * P.K + ki;
+      const float weight = P.gd[oi];
       const int* ind = reinterpret_cast<const int*>(P.inds) + oi * 3;
       const int p0 = bnd(t + ind[0], g.T);
       const int ph = ah + ind[1], pw = aw + ind[2];
@@ -93,100 +102,206 @@ __global__ void __launch_bounds__(128) search_bwd_kernel(const __grid_constant__
           red_add4(gkf + ko, a1);
         }
       }
-      continue;
     }
+  } else {
     // ---------------- float modes ----------------
-    const float* ind = reinterpret_cast<const float*>(P.inds) + oi * 3;
-    const float pp0 = (float)t + ind[0], pph = (float)ah + ind[1], ppw = (float)aw + ind[2];
-    float iw0 = 0.f, iw1 = 0.f;
-    int sHc = 1, sWc = 1, kj = 0;
-    int64_t ro = 0;
-    if (MODE >= 2) { iw0 = P.gi[oi * 3 + 1]; iw1 = P.gi[oi * 3 + 2]; }
-    if (MODE == 3) {
-      kj = P.kselect[oi];
-      ro = (((((int64_t)b * o.HD_f + hd_f) * g.Tq + tl) * g.nH + nh) * g.nW + nw) * o.Ks + kj;
-      sHc = P.reflect[ro * 2] ? -1 : 1;
-      sWc = P.reflect[ro * 2 + 1] ? -1 : 1;
-      if (c4 == 0) {
-        atomicAdd(P.gflows + ro * 3 + 1, sHc * iw0);
-        atomicAdd(P.gflows + ro * 3 + 2, sWc * iw1);
-      }
-    }
-    if (MODE >= 2) {
-      if (!(inb(pp0, g.T) && inb(pph, g.kH) && inb(ppw, g.kW))) continue;
-    }
-    const float p0 = bnd(pp0, g.T);
-    if (!inb(p0, g.T)) continue;
-    const int pt0 = __float2int_rn(p0);
-    const float* kf = kb + (int64_t)(pt0 - g.tk0) * kfs;
-    float* gkf = gkb + (int64_t)(pt0 - g.tk0) * kfs;
-    float dfw = 0.f, dfh = 0.f;  // accumulated d/d(flow_w), d/d(flow_h)
-#pragma unroll
-    for (int pi = 0; pi < ps; pi++) {
-      int d = o.dilation * (pi + o.patch_offset);
-      int r1 = rh + o.off_Hq + d;
-      float p1 = pph + (float)d;
-      const int signH = inb(p1, g.kH) ? 1 : -1;
-      if (o.reflect_bounds) { r1 = bnd(r1, g.qH); p1 = bnd(p1, g.kH); }
-      if (!(inb(r1, g.qH) && inb(p1, g.kH))) continue;
-#pragma unroll
-      for (int pj = 0; pj < ps; pj++) {
-        int e = o.dilation * (pj + o.patch_offset);
-        int r2 = rw + o.off_Wq + e;
-        float p2 = ppw + (float)e;
-        const int signW = inb(p2, g.kW) ? 1 : -1;
-        if (o.reflect_bounds) { r2 = bnd(r2, g.qW); p2 = bnd(p2, g.kW); }
-        if (!(inb(r2, g.qW) && inb(p2, g.kW))) continue;
-        const Taps tp = make_taps(p1, p2, g.kH, g.kW);
-        const int64_t qo = ((int64_t)r1 * g.qW + r2) * g.Fp;
-        const float4 x0 = ldg4(qf + qo);
-        const float4 x1 = interp4(kf - c4, tp, g.kW, g.Fp, c4);
-        float4 a0, a1;
-        if (DIST == 0) { a0 = f4scale(x1, weight); a1 = f4scale(x0, weight); }
-        else {
-          float w2 = weight * 2;
-          a0 = make_float4(w2 * (x0.x - x1.x), w2 * (x0.y - x1.y), w2 * (x0.z - x1.z), w2 * (x0.w - x1.w));
-          a1 = make_float4(-a0.x, -a0.y, -a0.z, -a0.w);
+    struct Pre {
+      float weight, pp0, pph, ppw, iw0, iw1;
+      int sHc, sWc, pt0;
+      int64_t ro;
+      bool valid;
+    };
+    // per-neighbour preamble; `first` = do the once-only index-gradient atomics of the refine layout
+    auto preamble = [&](int ki, bool first) {
+      Pre z;
+      const int64_t oi = wq * P.K + ki;
+      z.weight = P.gd[oi];
+      const float* ind = reinterpret_cast<const float*>(P.inds) + oi * 3;
+      z.pp0 = (float)t + ind[0]; z.pph = (float)ah + ind[1]; z.ppw = (float)aw + ind[2];
+      z.iw0 = z.iw1 = 0.f;
+      z.sHc = z.sWc = 1;
+      z.ro = 0;
+      z.pt0 = 0;
+      z.valid = false;
+      if (MODE >= 2) { z.iw0 = P.gi[oi * 3 + 1]; z.iw1 = P.gi[oi * 3 + 2]; }
+      if (MODE == 3) {
+        const int kj = P.kselect[oi];
+        z.ro = (((((int64_t)b * o.HD_f + hd_f) * g.Tq + tl) * g.nH + nh) * g.nW + nw) * o.Ks + kj;
+        z.sHc = P.reflect[z.ro * 2] ? -1 : 1;
+        z.sWc = P.reflect[z.ro * 2 + 1] ? -1 : 1;
+        if (first && c4 == 0) {
+          atomicAdd(P.gflows + z.ro * 3 + 1, z.sHc * z.iw0);
+          atomicAdd(P.gflows + z.ro * 3 + 2, z.sWc * z.iw1);
         }
-        if (PS > 0) { float4& A = acc[pi * PS + pj]; A.x += a0.x; A.y += a0.y; A.z += a0.z; A.w += a0.w; }
-        else red_add4(gqf + qo, a0);
+      }
+      if (MODE >= 2) {
+        if (!(inb(z.pp0, g.T) && inb(z.pph, g.kH) && inb(z.ppw, g.kW))) return z;
+      }
+      const float p0 = bnd(z.pp0, g.T);
+      if (!inb(p0, g.T)) return z;
+      z.pt0 = __float2int_rn(p0);
+      z.valid = true;
+      return z;
+    };
+    // flow-gradient tail of one neighbour (non_local_search_bilin2d_kernel.cu:555-594 ; shared_kernel.cu:1001-1026)
+    auto tail = [&](const Pre& z, float dfw, float dfh) {
+      if (MODE == 2) {
+        const int dt = (int)z.pp0 - t;
+        const int dto = time_tmax(t, g.T, o.wt) - t;
+        const int si = (dt >= 0) ? (dt - o.st_offset) : (dto - dt - o.st_offset);
+        if (si < 0) return;
+        const int nF = P.W_t - o.st_offset;
+        const int64_t fb = ((((int64_t)b * o.HD_f + hd_f) * g.Tq + tl) * nF + si) * 2;
+        const int64_t plane = (int64_t)g.nH * g.nW, off = (int64_t)nh * g.nW + nw;
+        const float hi = (float)ah + P.flows[(fb + 1) * plane + off];
+        const float wi = (float)aw + P.flows[fb * plane + off];
+        const int sH = inb(hi, g.kH) ? 1 : -1, sW = inb(wi, g.kW) ? 1 : -1;
+        float addw = sW * dfw, addh = sH * dfh;
+        if (c4 == 0) { addw += sW * z.iw1; addh += sH * z.iw0; }
+        atomicAdd(P.gflows + fb * plane + off, addw);
+        atomicAdd(P.gflows + (fb + 1) * plane + off, addh);
+      } else if (MODE == 3) {
+        atomicAdd(P.gflows + z.ro * 3 + 2, z.sWc * dfw);
+        atomicAdd(P.gflows + z.ro * 3 + 1, z.sHc * dfh);
+      }
+    };
+    // generic patch loop: every pixel validated / reflected on its own (nls_bilin2d.cu:95-291)
+    auto generic = [&](const Pre& z) {
+      const float weight = z.weight;
+      const float* kf = kb + (int64_t)(z.pt0 - g.tk0) * kfs;
+      float* gkf = gkb + (int64_t)(z.pt0 - g.tk0) * kfs;
+      float dfw = 0.f, dfh = 0.f;
 #pragma unroll
-        for (int ix = 0; ix < 2; ix++) {
+      for (int pi = 0; pi < ps; pi++) {
+        int d = o.dilation * (pi + o.patch_offset);
+        int r1 = rh + o.off_Hq + d;
+        float p1 = z.pph + (float)d;
+        const int signH = inb(p1, g.kH) ? 1 : -1;
+        if (o.reflect_bounds) { r1 = bnd(r1, g.qH); p1 = bnd(p1, g.kH); }
+        if (!(inb(r1, g.qH) && inb(p1, g.kH))) continue;
 #pragma unroll
-          for (int jx = 0; jx < 2; jx++) {
-            if (!tp.vh[ix] || !tp.vw[jx]) continue;
-            const int64_t ko = ((int64_t)tp.h[ix] * g.kW + tp.w[jx]) * g.Fp;
-            red_add4(gkf + ko, f4scale(a1, tp.gh[ix] * tp.gw[jx]));
-            if (MODE >= 2) {  // update_dFlows, shared_kernel.cu:916-964
-              const float4 v = ldg4(kf + ko);
-              const float dot = v.x * a1.x + v.y * a1.y + v.z * a1.z + v.w * a1.w;
-              const float gH = (jx == 0) ? -tp.gh[ix] : tp.gh[ix];
-              const float gW = (ix == 0) ? -tp.gw[jx] : tp.gw[jx];
-              dfw += gH * dot * signW;
-              dfh += gW * dot * signH;
+        for (int pj = 0; pj < ps; pj++) {
+          int e = o.dilation * (pj + o.patch_offset);
+          int r2 = rw + o.off_Wq + e;
+          float p2 = z.ppw + (float)e;
+          const int signW = inb(p2, g.kW) ? 1 : -1;
+          if (o.reflect_bounds) { r2 = bnd(r2, g.qW); p2 = bnd(p2, g.kW); }
+          if (!(inb(r2, g.qW) && inb(p2, g.kW))) continue;
+          const Taps tp = make_taps(p1, p2, g.kH, g.kW);
+          const int64_t qo = ((int64_t)r1 * g.qW + r2) * g.Fp;
+          const float4 x0 = ldg4(qf + qo);
+          const float4 x1 = interp4(kf - c4, tp, g.kW, g.Fp, c4);
+          float4 a0, a1;
+          if (DIST == 0) { a0 = f4scale(x1, weight); a1 = f4scale(x0, weight); }
+          else {
+            float w2 = weight * 2;
+            a0 = make_float4(w2 * (x0.x - x1.x), w2 * (x0.y - x1.y), w2 * (x0.z - x1.z), w2 * (x0.w - x1.w));
+            a1 = make_float4(-a0.x, -a0.y, -a0.z, -a0.w);
+          }
+          if (PS > 0) { float4& A = acc[pi * PS + pj]; A.x += a0.x; A.y += a0.y; A.z += a0.z; A.w += a0.w; }
+          else red_add4(gqf + qo, a0);
+#pragma unroll
+          for (int ix = 0; ix < 2; ix++) {
+#pragma unroll
+            for (int jx = 0; jx < 2; jx++) {
+              if (!tp.vh[ix] || !tp.vw[jx]) continue;
+              const int64_t ko = ((int64_t)tp.h[ix] * g.kW + tp.w[jx]) * g.Fp;
+              red_add4(gkf + ko, f4scale(a1, tp.gh[ix] * tp.gw[jx]));
+              if (MODE >= 2) {  // update_dFlows, shared_kernel.cu:916-964
+                const float4 v = ldg4(kf + ko);
+                const float dot = v.x * a1.x + v.y * a1.y + v.z * a1.z + v.w * a1.w;
+                const float gH = (jx == 0) ? -tp.gh[ix] : tp.gh[ix];
+                const float gW = (ix == 0) ? -tp.gw[jx] : tp.gw[jx];
+                dfw += gH * dot * signW;
+                dfh += gW * dot * signH;
+              }
             }
           }
         }
       }
-    }
-    if (MODE == 2) {  // non_local_search_bilin2d_kernel.cu:555-594
-      const int dt = (int)pp0 - t;
-      const int dto = time_tmax(t, g.T, o.wt) - t;
-      const int si = (dt >= 0) ? (dt - o.st_offset) : (dto - dt - o.st_offset);
-      if (si < 0) continue;
-      const int nF = P.W_t - o.st_offset;
-      const int64_t fb = ((((int64_t)b * o.HD_f + hd_f) * g.Tq + tl) * nF + si) * 2;
-      const int64_t plane = (int64_t)g.nH * g.nW, off = (int64_t)nh * g.nW + nw;
-      const float hi = (float)ah + P.flows[(fb + 1) * plane + off];
-      const float wi = (float)aw + P.flows[fb * plane + off];
-      const int sH = inb(hi, g.kH) ? 1 : -1, sW = inb(wi, g.kW) ? 1 : -1;
-      float addw = sW * dfw, addh = sH * dfh;
-      if (c4 == 0) { addw += sW * iw1; addh += sH * iw0; }
-      atomicAdd(P.gflows + fb * plane + off, addw);
-      atomicAdd(P.gflows + (fb + 1) * plane + off, addh);
-    } else if (MODE == 3) {  // bwd_flow_assign_v2, shared_kernel.cu:1001-1026
-      atomicAdd(P.gflows + ro * 3 + 2, sWc * dfw);
-      atomicAdd(P.gflows + ro * 3 + 1, sHc * dfh);
+      tail(z, dfw, dfh);
+    };
+
+    // footprint fast path (ps == 3, dilation == 1): the 9 bilinear reads of an interior neighbour
+    // patch share a 4x4 pixel footprint -> 16 loads + 16 vector REDs instead of 36 + 36.  Pairs that
+    // do not qualify are deferred (bit mask) so a warp does not run both paths for every k.
+    const int po = o.patch_offset;
+    const bool fast3 = FAST && (PS == 3) && P.fast3 && (P.K <= 32) && (o.off_Hq == 0) && (o.off_Wq == 0) &&
+                       (rh + po >= 0) && (rh + po + 2 <= g.qH - 1) && (rw + po >= 0) && (rw + po + 2 <= g.qW - 1);
+    if (!fast3) {
+      for (int ki = 0; ki < P.K; ki++) {
+        const Pre z = preamble(ki, true);
+        if (z.valid) generic(z);
+      }
+    } else {
+      unsigned slow = 0;
+      for (int ki = 0; ki < P.K; ki++) {
+        const Pre z = preamble(ki, true);
+        if (!z.valid) continue;
+        const int h0 = __float2int_rz(z.pph + (float)po), w0 = __float2int_rz(z.ppw + (float)po);
+        float gh[3][2], gw[3][2];
+        bool ok = true;
+#pragma unroll
+        for (int p = 0; p < 3; p++) {
+          const float n1 = z.pph + (float)(p + po), n2 = z.ppw + (float)(p + po);
+          const int a0 = __float2int_rz(n1), a1 = __float2int_rz(n1 + 1);
+          const int b0 = __float2int_rz(n2), b1 = __float2int_rz(n2 + 1);
+          ok = ok && (n1 >= 0) && (a0 == h0 + p) && (a1 == h0 + p + 1) && (a1 <= g.kH - 1);
+          ok = ok && (n2 >= 0) && (b0 == w0 + p) && (b1 == w0 + p + 1) && (b1 <= g.kW - 1);
+          gh[p][0] = fmaxf(0.f, 1 - fabsf(a0 - n1)); gh[p][1] = fmaxf(0.f, 1 - fabsf(a1 - n1));
+          gw[p][0] = fmaxf(0.f, 1 - fabsf(b0 - n2)); gw[p][1] = fmaxf(0.f, 1 - fabsf(b1 - n2));
+        }
+        if (!ok) { slow |= 1u << ki; continue; }
+        const float weight = z.weight;
+        const int64_t fo = (int64_t)(z.pt0 - g.tk0) * kfs + ((int64_t)h0 * g.kW + w0) * g.Fp;
+        const float* vr = kb + fo;
+        float* gr_ = gkb + fo;
+        const int64_t rs = (int64_t)g.kW * g.Fp;
+        float dfw = 0.f, dfh = 0.f;
+        float4 A[4], B[4], accA[4], accB[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) { A[j] = ldg4(vr + j * g.Fp); accA[j] = f4zero(); }
+#pragma unroll
+        for (int pi = 0; pi < 3; pi++) {
+#pragma unroll
+          for (int j = 0; j < 4; j++) { B[j] = ldg4(vr + (pi + 1) * rs + j * g.Fp); accB[j] = f4zero(); }
+#pragma unroll
+          for (int pj = 0; pj < 3; pj++) {
+            const float4 x0 = ldg4(qf + ((int64_t)(rh + pi + po) * g.qW + (rw + pj + po)) * g.Fp);
+            const float w00 = gh[pi][0] * gw[pj][0], w01 = gh[pi][0] * gw[pj][1];
+            const float w10 = gh[pi][1] * gw[pj][0], w11 = gh[pi][1] * gw[pj][1];
+            float4 x1 = f4zero();
+            fma4(x1, w00, A[pj]); fma4(x1, w01, A[pj + 1]); fma4(x1, w10, B[pj]); fma4(x1, w11, B[pj + 1]);
+            float4 a0, a1;
+            if (DIST == 0) { a0 = f4scale(x1, weight); a1 = f4scale(x0, weight); }
+            else {
+              const float w2 = weight * 2;
+              a0 = make_float4(w2 * (x0.x - x1.x), w2 * (x0.y - x1.y), w2 * (x0.z - x1.z), w2 * (x0.w - x1.w));
+              a1 = make_float4(-a0.x, -a0.y, -a0.z, -a0.w);
+            }
+            { float4& Aq = acc[(PS == 3) ? pi * 3 + pj : 0]; Aq.x += a0.x; Aq.y += a0.y; Aq.z += a0.z; Aq.w += a0.w; }
+            fma4(accA[pj], w00, a1); fma4(accA[pj + 1], w01, a1);
+            fma4(accB[pj], w10, a1); fma4(accB[pj + 1], w11, a1);
+            if (MODE >= 2) {  // update_dFlows, shared_kernel.cu:916-964 (all signs +1 in the interior)
+              const float d00 = dot4(A[pj], a1), d01 = dot4(A[pj + 1], a1);
+              const float d10 = dot4(B[pj], a1), d11 = dot4(B[pj + 1], a1);
+              dfw += gh[pi][0] * (d01 - d00) + gh[pi][1] * (d11 - d10);
+              dfh += gw[pj][0] * (d10 - d00) + gw[pj][1] * (d11 - d01);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 4; j++) { red_add4(gr_ + pi * rs + j * g.Fp, accA[j]); A[j] = B[j]; accA[j] = accB[j]; }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) red_add4(gr_ + 3 * rs + j * g.Fp, accA[j]);
+        tail(z, dfw, dfh);
+      }
+      while (slow) {
+        const int ki = __ffs(slow) - 1;
+        slow &= slow - 1;
+        const Pre z = preamble(ki, false);
+        if (z.valid) generic(z);
+      }
     }
   }
 
@@ -207,13 +322,15 @@ __global__ void __launch_bounds__(128) search_bwd_kernel(const __grid_constant__
   }
 }
 
+
 template <int MODE, int DIST>
 void launch_bwd(const BwdParams& P, cudaStream_t st) {
   const int tpb = 128;
   unsigned blocks = (unsigned)((P.nthreads + tpb - 1) / tpb);
-  if (P.o.ps == 1) search_bwd_kernel<MODE, DIST, 1><<<blocks, tpb, 0, st>>>(P);
-  else if (P.o.ps == 3) search_bwd_kernel<MODE, DIST, 3><<<blocks, tpb, 0, st>>>(P);
-  else search_bwd_kernel<MODE, DIST, 0><<<blocks, tpb, 0, st>>>(P);
+  if (P.o.ps == 1) search_bwd_kernel<MODE, DIST, 1, false><<<blocks, tpb, 0, st>>>(P);
+  else if (P.o.ps == 3 && P.fast3 && MODE != 0) search_bwd_kernel<MODE, DIST, 3, true><<<blocks, tpb, 0, st>>>(P);
+  else if (P.o.ps == 3) search_bwd_kernel<MODE, DIST, 3, false><<<blocks, tpb, 0, st>>>(P);
+  else search_bwd_kernel<MODE, DIST, 0, false><<<blocks, tpb, 0, st>>>(P);
 }
 
 }  // namespace
@@ -230,6 +347,7 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   P.gq = gq_cl; P.gk = gk_cl; P.gflows = grad_flows; P.q = q_cl; P.k = k_cl; P.flows = flows;
   P.gd = grad_dists; P.gi = grad_inds; P.inds = inds; P.kselect = kselect; P.reflect = reflect;
   P.g = *g; P.o = *o; P.K = K; P.nquad = g->Fp / 4; P.W_t = 2 * o->wt + 1;
+  P.fast3 = (o->ps == 3 && o->dilation == 1 && getenv("STNLS_BWD_FAST3")) ? 1 : 0;  // opt-in: measured slower
   const bool refine = o->wr > 0;
   if (o->itype_int) P.mode = 0;
   else if (!grad_flows) P.mode = 1;

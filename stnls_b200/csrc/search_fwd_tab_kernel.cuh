@@ -31,6 +31,31 @@ __device__ __forceinline__ float ord2f(unsigned u) {
   return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
+// shared-memory accessors on 32-bit shared-window byte addresses (keeps address math to one IADD/IMAD)
+__device__ __forceinline__ float4 lds4(unsigned a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts4(unsigned a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ unsigned lds1(unsigned a) {
+  unsigned v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts1(unsigned a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ldsh(unsigned a) {
+  unsigned short v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+  return v;
+}
+// 16-byte read-only global load at base + 32-bit byte offset
+__device__ __forceinline__ float4 ldg4b(const char* base, unsigned off) {
+  return __ldg(reinterpret_cast<const float4*>(base + off));
+}
+
 __device__ __forceinline__ void fma4(float4& v, float w, const float4 t) {
   v.x = fmaf(w, t.x, v.x); v.y = fmaf(w, t.y, v.y); v.z = fmaf(w, t.z, v.z); v.w = fmaf(w, t.w, v.w);
 }
@@ -38,15 +63,15 @@ __device__ __forceinline__ void fma4(float4& v, float w, const float4 t) {
 // key value at one lattice point: plain read (int) or 4-tap bilinear, taps outside the frame dropped
 // (shared_kernel.cu:738-771; tap order (0,0),(0,1),(1,0),(1,1) and weight gh*gw as in the reference)
 template <bool INT>
-__device__ __forceinline__ float4 lattice_value(const float* kc, const float4 eh, const float4 ew) {
-  const int oh0 = __float_as_int(eh.x), ow0 = __float_as_int(ew.x);
-  if (INT) return ldg4(kc + (unsigned)(oh0 + ow0));
+__device__ __forceinline__ float4 lattice_value(const char* kc, const float4 eh, const float4 ew) {
+  const int oh0 = __float_as_int(eh.x), ow0 = __float_as_int(ew.x);   // byte offsets, < 0: tap outside
+  if (INT) return ldg4b(kc, (unsigned)(oh0 + ow0));
   const int oh1 = __float_as_int(eh.y), ow1 = __float_as_int(ew.y);
   float4 v = f4zero();
-  if ((oh0 | ow0) >= 0) fma4(v, eh.z * ew.z, ldg4(kc + (unsigned)(oh0 + ow0)));
-  if ((oh0 | ow1) >= 0) fma4(v, eh.z * ew.w, ldg4(kc + (unsigned)(oh0 + ow1)));
-  if ((oh1 | ow0) >= 0) fma4(v, eh.w * ew.z, ldg4(kc + (unsigned)(oh1 + ow0)));
-  if ((oh1 | ow1) >= 0) fma4(v, eh.w * ew.w, ldg4(kc + (unsigned)(oh1 + ow1)));
+  if ((oh0 | ow0) >= 0) fma4(v, eh.z * ew.z, ldg4b(kc, (unsigned)(oh0 + ow0)));
+  if ((oh0 | ow1) >= 0) fma4(v, eh.z * ew.w, ldg4b(kc, (unsigned)(oh0 + ow1)));
+  if ((oh1 | ow0) >= 0) fma4(v, eh.w * ew.z, ldg4b(kc, (unsigned)(oh1 + ow0)));
+  if ((oh1 | ow1) >= 0) fma4(v, eh.w * ew.w, ldg4b(kc, (unsigned)(oh1 + ow1)));
   return v;
 }
 
@@ -56,9 +81,7 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
                                                                 const __grid_constant__ TabCfg C) {
   typedef typename CT<INT>::type CC;
   extern __shared__ float4 smem4[];
-  int* const smi = reinterpret_cast<int*>(smem4);
-  unsigned* const smu = reinterpret_cast<unsigned*>(smem4);
-  const unsigned short* const dec = reinterpret_cast<const unsigned short*>(smem4);
+  const unsigned sb = (unsigned)__cvta_generic_to_shared(smem4);  // all smem traffic goes through lds*/sts* on sb
   const stnls_geom& g = P.g;
   const stnls_search_opts& o = P.o;
   const int lane = threadIdx.x & 31;
@@ -70,7 +93,7 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
   // per-CTA decode table of the lattice points: x -> (mh << 8) | mw
   for (int x = threadIdx.x; x < M * M; x += blockDim.x) {
     int mh = fdiv(x, C.inv_M);
-    reinterpret_cast<unsigned short*>(smem4)[x] = (unsigned short)((mh << 8) | (x - mh * M));
+    reinterpret_cast<unsigned short*>(smem4)[x] = (unsigned short)((mh << 8) | (x - mh * M));  // plain store, before the barrier
   }
   __syncthreads();
 
@@ -128,7 +151,7 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
       int p = (Q4T > 0 || C.q4sh >= 0) ? (it >> C.q4sh) : fdiv(it, C.inv_Q4);
       int c4 = it - p * Q4;
       int po = __shfl_sync(FULL_MASK, qo, p & 31);
-      if (it < ps2 * Q4 && ((qmask >> p) & 1)) smem4[qb + it] = ldg4(qf + po + c4 * 4);
+      if (it < ps2 * Q4 && ((qmask >> p) & 1)) sts4(sb + (qb + it) * 16, ldg4(qf + po + c4 * 4));
     }
   }
   const bool qfull = qmask == ((ps2 >= 32) ? 0xffffffffu : ((1u << ps2) - 1u));
@@ -174,13 +197,13 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
 
   // -- pass 2: per batch of groups: axis tables -> lattice table -> candidate distances --
   const CC s1c = INT ? (CC)(int)o.stride1 : (CC)o.stride1;
-  const int rowsc = g.kW * g.Fp;  // floats per key row
+  const int rowsc = g.kW * g.Fp * 4;  // bytes per key row
   for (int g0 = 0; g0 < P.nG; g0 += C.nb) {
     const int nbg = min(C.nb, P.nG - g0);
     Group<CC> mine = group_params<INT, REFINE>(P, c, g0 + min(lane, nbg - 1));
     int my_ag = 0;
     if (REFINE && anchored) my_ag = refine_group_anchor<CC>(P, c, mine, g0 + min(lane, nbg - 1));
-    if (lane < nbg) smi[gfrb + lane] = (mine.ok && inb(mine.t, g.T)) ? (mine.t - g.tk0) : -1;
+    if (lane < nbg) sts1(sb + (gfrb + lane) * 4, (unsigned)((mine.ok && inb(mine.t, g.T)) ? (mine.t - g.tk0) : -1));
     // 1. axis tables: one 32-lane round per group (both axes, M <= 16) or per (group, axis)
     for (int rd = 0; rd < nbg * C.ax_rounds; rd++) {
       int gl, axis, m;
@@ -188,7 +211,7 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
       else { gl = rd >> 1; axis = rd & 1; m = lane; }
       Group<CC> gp = shfl_group(mine, gl);
       const int lim = axis ? g.kW : g.kH;
-      const int sc = axis ? g.Fp : rowsc;
+      const int sc = axis ? g.Fp * 4 : rowsc;
       const CC a = axis ? gp.aw : gp.ah, off = axis ? gp.offw : gp.offh;
       bool pv = false;
       int o0 = -1, o1 = -1;
@@ -210,43 +233,46 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
           o0 = inb(t0, lim) ? t0 * sc : -1;
           o1 = inb(t1, lim) ? t1 * sc : -1;
         }
-        smem4[axb + (gl * 2 + axis) * M + m] = make_float4(__int_as_float(o0), __int_as_float(o1), w0, w1);
+        sts4(sb + (axb + (gl * 2 + axis) * M + m) * 16, make_float4(__int_as_float(o0), __int_as_float(o1), w0, w1));
       }
       unsigned bal = __ballot_sync(FULL_MASK, pv);
       if (lane == 0) {
-        if (C.ax_rounds == 1) { smu[mskb + gl * 2] = bal & 0xffffu; smu[mskb + gl * 2 + 1] = bal >> 16; }
-        else smu[mskb + gl * 2 + axis] = bal;
+        if (C.ax_rounds == 1) { sts1(sb + (mskb + gl * 2) * 4, bal & 0xffffu); sts1(sb + (mskb + gl * 2 + 1) * 4, bal >> 16); }
+        else sts1(sb + (mskb + gl * 2 + axis) * 4, bal);
       }
     }
     __syncwarp();
     // 2. lattice table: item = (mh, mw, channel quad), quads fastest so a warp reads whole pixels
     const int MM = M * M;
     for (int gl = 0; gl < nbg; gl++) {
-      const int fr = smi[gfrb + gl];
+      const int fr = (int)lds1(sb + (gfrb + gl) * 4);
       if (fr < 0) continue;
-      const unsigned mh_ok = smu[mskb + gl * 2], mw_ok = smu[mskb + gl * 2 + 1];
-      const int Ah = axb + (gl * 2) * M, Aw = Ah + M;
+      const unsigned mh_ok = lds1(sb + (mskb + gl * 2) * 4), mw_ok = lds1(sb + (mskb + gl * 2 + 1) * 4);
+      const unsigned Ah = sb + (axb + (gl * 2) * M) * 16, Aw = Ah + M * 16;
       const int Tg = Tb + gl * C.GS4;
-      const float* kf = kbase + (int64_t)fr * kfs;
+      const char* kf = reinterpret_cast<const char*>(kbase + (int64_t)fr * kfs);
       if (Q4T > 0) {  // 32 % Q4T == 0: the channel quad of a lane never changes
         const int c4 = lane & (Q4T - 1);
-        const float* kc = kf + c4 * 4;
-        const int Tgc = Tg + c4 * C.PS4;
+        const char* kc = kf + c4 * 16;
+        asm volatile("" : "+l"(kc));  // keep the frame pointer in registers (no re-derivation per tap)
+        const unsigned Tgc = sb + (Tg + c4 * C.PS4) * 16;
+        const unsigned Mp16 = C.Mp * 16;
         for (int x = lane / Q4T; x < MM; x += 32 / Q4T) {
-          const unsigned d = dec[x];
-          const int mh = d >> 8, mw = d & 255;
+          const unsigned d = ldsh(sb + x * 2);
+          const unsigned mh = d >> 8, mw = d & 255;
           if (!(((mh_ok >> mh) & (mw_ok >> mw)) & 1)) continue;
-          smem4[Tgc + mh * C.Mp + mw] = lattice_value<INT>(kc, smem4[Ah + mh], smem4[Aw + mw]);
+          sts4(Tgc + mh * Mp16 + mw * 16, lattice_value<INT>(kc, lds4(Ah + mh * 16), lds4(Aw + mw * 16)));
         }
       } else {
         for (int it = lane; it < MM * Q4; it += 32) {
           int x, c4;
           if (C.q4sh >= 0) { x = it >> C.q4sh; c4 = it & (Q4 - 1); }
           else { x = fdiv(it, C.inv_Q4); c4 = it - x * Q4; }
-          const unsigned d = dec[x];
-          const int mh = d >> 8, mw = d & 255;
+          const unsigned d = ldsh(sb + x * 2);
+          const unsigned mh = d >> 8, mw = d & 255;
           if (!(((mh_ok >> mh) & (mw_ok >> mw)) & 1)) continue;
-          smem4[Tg + c4 * C.PS4 + mh * C.Mp + mw] = lattice_value<INT>(kf + c4 * 4, smem4[Ah + mh], smem4[Aw + mw]);
+          sts4(sb + (Tg + c4 * C.PS4 + mh * C.Mp + mw) * 16,
+               lattice_value<INT>(kf + c4 * 16, lds4(Ah + mh * 16), lds4(Aw + mw * 16)));
         }
       }
     }
@@ -273,8 +299,9 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
       }
       const bool cvalid = active && gp.ok && inb(gp.t, g.T) && inb(chh, g.kH) && inb(cww, g.kW);
       const int mh0 = C.n1 * wi, mw0 = C.n1 * wj;
-      const unsigned hm = smu[mskb + gl * 2] >> mh0, wm = smu[mskb + gl * 2 + 1] >> mw0;
-      const int Tc = Tb + gl * C.GS4 + mh0 * C.Mp + mw0;
+      const unsigned hm = lds1(sb + (mskb + gl * 2) * 4) >> mh0, wm = lds1(sb + (mskb + gl * 2 + 1) * 4) >> mw0;
+      const unsigned Tc = sb + (Tb + gl * C.GS4 + mh0 * C.Mp + mw0) * 16;
+      const unsigned qa = sb + qb * 16, rstep = C.n2 * C.Mp * 16, cstep = C.n2 * 16, pstep = C.PS4 * 16;
       const bool allpix = qfull && ((hm & C.rpat) == C.rpat) && ((wm & C.rpat) == C.rpat);
       float d = invalid;
       if (__all_sync(FULL_MASK, allpix || !cvalid)) {
@@ -285,10 +312,10 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
           for (int pi = 0; pi < ps; pi++) {
 #pragma unroll
             for (int pj = 0; pj < ps; pj++) {
-              const int tp = Tc + C.n2 * (pi * C.Mp + pj);
-              const int qp = qb + (pi * ps + pj) * Q4;
+              const unsigned tp = Tc + pi * rstep + pj * cstep;
+              const unsigned qp = qa + (pi * ps + pj) * Q4 * 16;
 #pragma unroll
-              for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, smem4[qp + c4], smem4[tp + c4 * C.PS4]);
+              for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, lds4(qp + c4 * 16), lds4(tp + c4 * pstep));
             }
           }
           d = dist;
@@ -299,9 +326,9 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
           if (!((hm >> (C.n2 * pi)) & 1)) continue;
           for (int pj = 0; pj < ps; pj++) {
             if (!(((wm >> (C.n2 * pj)) & (qmask >> (pi * ps + pj))) & 1)) continue;
-            const int tp = Tc + C.n2 * (pi * C.Mp + pj);
-            const int qp = qb + (pi * ps + pj) * Q4;
-            for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, smem4[qp + c4], smem4[tp + c4 * C.PS4]);
+            const unsigned tp = Tc + pi * rstep + pj * cstep;
+            const unsigned qp = qa + (pi * ps + pj) * Q4 * 16;
+            for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, lds4(qp + c4 * 16), lds4(tp + c4 * pstep));
           }
         }
         d = dist;
@@ -328,7 +355,7 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
         if (keep_all) continue;
       }
       if (active && !(anchored && eff == 0))
-        smu[keyb + eff] = min(f2ord(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu);
+        sts1(sb + (keyb + eff) * 4, min(f2ord(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu));
     }
     __syncwarp();
   }
@@ -340,7 +367,7 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
   unsigned bk = 0xffffffffu;
   int bi = 0x7fffffff;
   for (int i = start; i < P.L; i += 32) {
-    unsigned kv = smu[keyb + i];
+    unsigned kv = lds1(sb + (keyb + i) * 4);
     if (kv < bk) { bk = kv; bi = i; }
   }
   unsigned mykey = 0xffffffffu;
@@ -351,11 +378,11 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
     const int widx = (int)__reduce_min_sync(FULL_MASK, (bk == m) ? (unsigned)bi : 0x7fffffffu);
     if (lane == kk) { mykey = m; mypos = widx; }
     if (bi == widx) {
-      smu[keyb + bi] = 0xffffffffu;
+      sts1(sb + (keyb + bi) * 4, 0xffffffffu);
       bk = 0xffffffffu;
       bi = 0x7fffffff;
       for (int i = start; i < P.L; i += 32) {
-        unsigned kv = smu[keyb + i];
+        unsigned kv = lds1(sb + (keyb + i) * 4);
         if (kv < bk) { bk = kv; bi = i; }
       }
     }

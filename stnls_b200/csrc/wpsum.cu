@@ -8,6 +8,7 @@
 // patch-overlap count fused in.  The backward keeps grad_weights / grad_flows in registers and
 // scatters grad_v with 16-byte vector REDs.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -89,8 +90,18 @@ __global__ void __launch_bounds__(128) wpsum_fwd_kernel(const __grid_constant__ 
   *reinterpret_cast<float4*>(P.out + (((int64_t)n * g.Tq + tl) * H + h) * W * g.Fp + (int64_t)w * g.Fp + c4) = o4;
 }
 
-template <bool INT>
-__global__ void __launch_bounds__(128) wpsum_bwd_kernel(const __grid_constant__ AggParams P) {
+__device__ __forceinline__ float dot4(const float4 a, const float4 b) {
+  return fmaf(a.w, b.w, fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)));
+}
+__device__ __forceinline__ void axpy4(float4& y, float a, const float4 x) {
+  y.x = fmaf(a, x.x, y.x); y.y = fmaf(a, x.y, y.y); y.z = fmaf(a, x.z, y.z); y.w = fmaf(a, x.w, y.w);
+}
+
+// FAST3: ps == 3 && dilation == 1.  The 9 bilinear reads of one neighbour patch then share a 4x4
+// pixel footprint (all patch pixels have the same fractional position), so an interior (query, k)
+// pair reads 16 value pixels and issues 16 vector REDs instead of 36 + 36.
+template <bool INT, bool FAST3>
+__global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant__ AggParams P) {
   const stnls_geom& g = P.g;
   const stnls_agg_opts& o = P.o;
   const int H = g.kH, W = g.kW;
@@ -109,16 +120,19 @@ __global__ void __launch_bounds__(128) wpsum_bwd_kernel(const __grid_constant__ 
   const float* vb = P.v + (int64_t)n * g.Tk * vfs + c4;
   float* gvb = P.out + (int64_t)n * g.Tk * vfs + c4;
   const float* gof = P.gout + ((int64_t)n * g.Tq + tl) * vfs + c4;
-  for (int ki = 0; ki < o.K; ki++) {
+
+  // generic path for one neighbour: every patch pixel validated / reflected on its own
+  // (gather_add_kernel.cu:201-319 int, :369-514 + shared_kernel.cu:773-827 float)
+  auto generic = [&](int ki) {
     const int64_t oi = wq * o.K + ki;
     const float weight = P.weights[oi];
     float accw = 0.f, fh = 0.f, fw = 0.f;
     if (INT) {
       const int* f = reinterpret_cast<const int*>(P.flows) + oi * 3;
       int n0 = t + f[0], c1 = rh + f[1], c2 = rw + f[2];
-      if (!((abs(c1) < 1e7) && (abs(c2) < 1e7))) continue;
+      if (!((abs(c1) < 1e7) && (abs(c2) < 1e7))) return;
       n0 = bnd(n0, g.T); c1 = bnd(c1, H); c2 = bnd(c2, W);
-      if (!inb(n0, g.T)) continue;
+      if (!inb(n0, g.T)) return;
       const float* vf = vb + (int64_t)(n0 - g.tk0) * vfs;
       float* gvf = gvb + (int64_t)(n0 - g.tk0) * vfs;
       for (int pi = 0; pi < o.ps; pi++) {
@@ -143,13 +157,13 @@ __global__ void __launch_bounds__(128) wpsum_bwd_kernel(const __grid_constant__ 
     } else {
       const float* f = reinterpret_cast<const float*>(P.flows) + oi * 3;
       float n0 = (float)t + f[0], c1 = (float)rh + f[1], c2 = (float)rw + f[2];
-      if (!((fabsf(c1) < 1e7) && (fabsf(c2) < 1e7))) continue;
+      if (!((fabsf(c1) < 1e7) && (fabsf(c2) < 1e7))) return;
       n0 = bnd(n0, g.T);
       const int sH0 = inb(c1, H) ? 1 : -1;
       c1 = bnd(c1, H);
       const int sW0 = inb(c2, W) ? 1 : -1;
       c2 = bnd(c2, W);
-      if (!inb(n0, g.T)) continue;
+      if (!inb(n0, g.T)) return;
       const int nti = (int)n0;
       const float* vf = vb + (int64_t)(nti - g.tk0) * vfs;
       float* gvf = gvb + (int64_t)(nti - g.tk0) * vfs;
@@ -195,8 +209,91 @@ __global__ void __launch_bounds__(128) wpsum_bwd_kernel(const __grid_constant__ 
       atomicAdd(P.gflows + oi * 3 + 1, fh);
       atomicAdd(P.gflows + oi * 3 + 2, fw);
     }
+  };
+
+  if (!FAST3) {
+    for (int ki = 0; ki < o.K; ki++) generic(ki);
+    return;
+  }
+
+  // FAST3 (float, ps == 3, dilation == 1): interior (query, k) pairs take the footprint path; the
+  // others are deferred (bit mask) and handled afterwards so a warp does not run both paths per k
+  const int po = o.patch_offset;
+  const bool refok = (rh + po >= 0) && (rh + po + 2 <= H - 1) && (rw + po >= 0) && (rw + po + 2 <= W - 1);
+  if (!refok || o.K > 32) {
+    for (int ki = 0; ki < o.K; ki++) generic(ki);
+    return;
+  }
+  float4 grp[9];  // the query's own 3x3 patch of grad_out, read once for all K neighbours
+#pragma unroll
+  for (int pi = 0; pi < 3; pi++)
+#pragma unroll
+    for (int pj = 0; pj < 3; pj++) grp[pi * 3 + pj] = ldg4(gof + ((int64_t)(rh + pi + po) * W + (rw + pj + po)) * g.Fp);
+  unsigned slow = 0;
+  for (int ki = 0; ki < o.K; ki++) {
+    const int64_t oi = wq * o.K + ki;
+    const float* f = reinterpret_cast<const float*>(P.flows) + oi * 3;
+    float n0 = (float)t + f[0], c1 = (float)rh + f[1], c2 = (float)rw + f[2];
+    // centre inside the frame (no reflection) and every tap of the 3x3 patch inside a 4x4 footprint
+    n0 = bnd(n0, g.T);
+    bool ok = inb(n0, g.T) && (c1 >= 0) && (c2 >= 0) && (c1 <= (float)(H - 1)) && (c2 <= (float)(W - 1));
+    const int h0 = __float2int_rz(c1 + (float)po), w0 = __float2int_rz(c2 + (float)po);
+    float gh[3][2], gw[3][2];
+#pragma unroll
+    for (int p = 0; p < 3; p++) {
+      const float n1 = c1 + (float)(p + po), n2 = c2 + (float)(p + po);
+      const int a0 = __float2int_rz(n1), a1 = __float2int_rz(n1 + 1);
+      const int b0 = __float2int_rz(n2), b1 = __float2int_rz(n2 + 1);
+      ok = ok && (n1 >= 0) && (a0 == h0 + p) && (a1 == h0 + p + 1) && (a1 <= H - 1);
+      ok = ok && (n2 >= 0) && (b0 == w0 + p) && (b1 == w0 + p + 1) && (b1 <= W - 1);
+      gh[p][0] = fmaxf(0.f, 1 - fabsf(a0 - n1)); gh[p][1] = fmaxf(0.f, 1 - fabsf(a1 - n1));
+      gw[p][0] = fmaxf(0.f, 1 - fabsf(b0 - n2)); gw[p][1] = fmaxf(0.f, 1 - fabsf(b1 - n2));
+    }
+    if (!ok) { slow |= 1u << ki; continue; }
+    const float weight = P.weights[oi];
+    const int nti = (int)n0;
+    const int64_t fo = (int64_t)(nti - g.tk0) * vfs + ((int64_t)h0 * W + w0) * g.Fp;
+    const float* vr = vb + fo;
+    float* gr_ = gvb + fo;
+    const int64_t rs = (int64_t)W * g.Fp;
+    float4 A[4], B[4], accA[4], accB[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) { A[j] = ldg4(vr + j * g.Fp); accA[j] = f4zero(); }
+    float accw = 0.f, aH = 0.f, aW = 0.f;
+#pragma unroll
+    for (int pi = 0; pi < 3; pi++) {
+#pragma unroll
+      for (int j = 0; j < 4; j++) { B[j] = ldg4(vr + (pi + 1) * rs + j * g.Fp); accB[j] = f4zero(); }
+#pragma unroll
+      for (int pj = 0; pj < 3; pj++) {
+        const float4 gr = grp[pi * 3 + pj];
+        const float d00 = dot4(gr, A[pj]), d01 = dot4(gr, A[pj + 1]);
+        const float d10 = dot4(gr, B[pj]), d11 = dot4(gr, B[pj + 1]);
+        const float w00 = gh[pi][0] * gw[pj][0], w01 = gh[pi][0] * gw[pj][1];
+        const float w10 = gh[pi][1] * gw[pj][0], w11 = gh[pi][1] * gw[pj][1];
+        accw += w00 * d00 + w01 * d01 + w10 * d10 + w11 * d11;
+        aW += gh[pi][0] * (d01 - d00) + gh[pi][1] * (d11 - d10);
+        aH += gw[pj][0] * (d10 - d00) + gw[pj][1] * (d11 - d01);
+        const float4 wg = f4scale(gr, weight);
+        axpy4(accA[pj], w00, wg); axpy4(accA[pj + 1], w01, wg);
+        axpy4(accB[pj], w10, wg); axpy4(accB[pj + 1], w11, wg);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) { red_add4(gr_ + pi * rs + j * g.Fp, accA[j]); A[j] = B[j]; accA[j] = accB[j]; }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) red_add4(gr_ + 3 * rs + j * g.Fp, accA[j]);
+    atomicAdd(P.gweights + oi, accw);
+    atomicAdd(P.gflows + oi * 3 + 1, weight * aH);
+    atomicAdd(P.gflows + oi * 3 + 2, weight * aW);
+  }
+  while (slow) {
+    const int ki = __ffs(slow) - 1;
+    slow &= slow - 1;
+    generic(ki);
   }
 }
+
 
 int agg_check(const stnls_geom* g, const stnls_agg_opts* o, const char* who) {
   STNLS_REQUIRE(g && o, "%s: null argument", who);
@@ -241,8 +338,10 @@ extern "C" int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* gr
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_backward: too many threads for one launch");
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
   cudaStream_t st = (cudaStream_t)stream;
-  if (o->itype_int) wpsum_bwd_kernel<true><<<blocks, 128, 0, st>>>(P);
-  else wpsum_bwd_kernel<false><<<blocks, 128, 0, st>>>(P);
+  const bool fast3 = (o->ps == 3 && o->dilation == 1 && !getenv("STNLS_NO_FAST3"));
+  if (o->itype_int) wpsum_bwd_kernel<true, false><<<blocks, 128, 0, st>>>(P);
+  else if (fast3) wpsum_bwd_kernel<false, true><<<blocks, 128, 0, st>>>(P);
+  else wpsum_bwd_kernel<false, false><<<blocks, 128, 0, st>>>(P);
   STNLS_CHECK_LAUNCH("wpsum_backward");
   return STNLS_OK;
 }
