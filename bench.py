@@ -203,7 +203,7 @@ def run_product(args):
                                               dist_type=wl["dist_type"], self_action=wl["self_action"],
                                               itype=wl["itype"])
     agg = stnls_b200.agg.WeightedPatchSum(ps=wl["ps"], stride0=wl["stride0"], itype=wl["itype"])
-    model = parallel.ShardedSearchAgg(search, agg, plan, scale=wl["scale"])
+    model = parallel.ShardedSearchAgg(search, agg, plan, scale=wl["scale"], halo=args.halo)
 
     host = make_inputs(wl, rank, world, pin=True)
     flt = wl["itype"] == "float"
@@ -273,7 +273,7 @@ def run_product(args):
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     t_ms, e2e_ms = float(tt[0]), float(tt[1])
-    return dict(world=world, rank=rank, wl=wl, plan=plan, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
+    return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
                 launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h)
 
 
@@ -363,6 +363,7 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--halo", default="auto", choices=["auto", "peer", "nccl"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup
 
@@ -410,7 +411,7 @@ def main():
     line = {"metric": "search+agg fwd+bwd throughput", "value": value, "unit": "Gcandidates/s",
             "n_gpus": world, "steps": steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": describe(wl, args.workload, world),
+            "data": "synthetic", "config": dict(describe(wl, args.workload, world), halo=r["halo"]),
             "frames_per_s": wl["B"] * wl["T"] * world / (ms_per_step * 1e-3),
             "e2e": {"value": e2e_val, "unit": "Gcandidates/s", "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"], "ms_per_step": e2e_ms,

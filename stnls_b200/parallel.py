@@ -147,9 +147,95 @@ class HaloExchange(th.autograd.Function):
         return _exchange_backward(gext.contiguous(), ctx.plan, ctx.group), None, None
 
 
-def halo_exchange(x, plan, group=None):
+class PeerHalo:
+    """Halo exchange through NVLink **peer memory** instead of NCCL send/recv.
+
+    Every rank stages its frames in a symmetric-memory buffer (torch.distributed._symmetric_memory:
+    CUDA VMM allocations mapped into every rank of the node); after ONE device-side barrier on the
+    signal pads each rank pulls exactly the halo frames it needs straight out of its neighbours'
+    buffers with ordinary copy kernels (P2P loads over NVLink / NVSwitch).  Backward: the extended
+    gradient is staged the same way and each owner pulls-and-adds the slices it lent out.  Buffers are
+    persistent and double-buffered, so an exchange costs one barrier (a few microseconds) plus the
+    copies, against four NCCL P2P launches with their stream hand-offs."""
+
+    def __init__(self, plan, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.symm_mem = symm_mem
+        self.plan = plan
+        self.group = dist.group.WORLD if group is None else group
+        self.bufs = {}
+        self.count = {}
+        self.max_own = max(b - a for a, b in plan.owned)
+        self.max_ext = max(fb - fa for fa, fb in plan.need)
+        # probe now (allocation + rendezvous + barrier) so an unsupported box fails here, not mid-step
+        dev = th.device("cuda", th.cuda.current_device())
+        probe = symm_mem.empty((16,), dtype=th.float32, device=dev)
+        symm_mem.rendezvous(probe, self.group).barrier(channel=0)
+        th.cuda.synchronize()
+
+    def _buffers(self, tag, nframes, frame_shape, dtype, device):
+        key = (tag, nframes, tuple(frame_shape), dtype)
+        if key not in self.bufs:
+            pair = []
+            for _ in range(2):
+                t = self.symm_mem.empty((nframes,) + tuple(frame_shape), dtype=dtype, device=device)
+                pair.append((t, self.symm_mem.rendezvous(t, self.group)))
+            self.bufs[key] = pair
+            self.count[key] = 0
+        i = self.count[key]
+        self.count[key] = i + 1
+        return self.bufs[key][i % 2]
+
+    def forward(self, x, tag):
+        plan, td = self.plan, _time_dim(x)
+        xt = x.movedim(td, 0)                        # (T_own, ...) view, time major
+        frame_shape = tuple(xt.shape[1:])
+        buf, hdl = self._buffers(("f", tag), self.max_own, frame_shape, x.dtype, x.device)
+        buf[:plan.b - plan.a].copy_(xt)
+        hdl.barrier(channel=0)
+        shape = list(x.shape)
+        shape[td] = plan.fb - plan.fa
+        ext = x.new_empty(shape)
+        ext.narrow(td, plan.a - plan.fa, plan.b - plan.a).copy_(x)
+        for src, lo, hi in plan.recvs():
+            a_src = plan.owned[src][0]
+            peer = hdl.get_buffer(src, (self.max_own,) + frame_shape, x.dtype)
+            ext.narrow(td, lo - plan.fa, hi - lo).copy_(peer[lo - a_src:hi - a_src].movedim(0, td))
+        return ext
+
+    def backward(self, gext, tag):
+        plan, td = self.plan, _time_dim(gext)
+        gt = gext.movedim(td, 0)
+        frame_shape = tuple(gt.shape[1:])
+        buf, hdl = self._buffers(("b", tag), self.max_ext, frame_shape, gext.dtype, gext.device)
+        buf[:plan.fb - plan.fa].copy_(gt)
+        hdl.barrier(channel=0)
+        gown = gext.narrow(td, plan.a - plan.fa, plan.b - plan.a).contiguous()
+        for dst, lo, hi in plan.sends():              # frames we lent to dst: their gradient sits in dst's buffer
+            fa_dst = plan.need[dst][0]
+            peer = hdl.get_buffer(dst, (self.max_ext,) + frame_shape, gext.dtype)
+            gown.narrow(td, lo - plan.a, hi - lo).add_(peer[lo - fa_dst:hi - fa_dst].movedim(0, td))
+        return gown
+
+
+class PeerHaloExchange(th.autograd.Function):
+    """HaloExchange over peer memory (see PeerHalo)."""
+
+    @staticmethod
+    def forward(ctx, x, peer, tag):
+        ctx.peer, ctx.tag = peer, tag
+        return peer.forward(x.contiguous(), tag)
+
+    @staticmethod
+    def backward(ctx, gext):
+        return ctx.peer.backward(gext.contiguous(), ctx.tag), None, None
+
+
+def halo_exchange(x, plan, group=None, peer=None, tag="x"):
     if plan.world == 1:
         return x
+    if peer is not None:
+        return PeerHaloExchange.apply(x, peer, tag)
     return HaloExchange.apply(x, plan, group)
 
 
@@ -160,13 +246,23 @@ class ShardedSearchAgg(th.nn.Module):
     Returns the owned frames of the aggregated video (B,HD,T_own,F_head,H,W), dists and inds.
     """
 
-    def __init__(self, search, agg, plan, scale=10.0, group=None):
+    def __init__(self, search, agg, plan, scale=10.0, group=None, halo="auto"):
+        """halo: "peer" (NVLink peer memory, see PeerHalo), "nccl" (send/recv) or "auto" (peer when available)."""
         super().__init__()
         self.search, self.agg, self.plan, self.scale, self.group = search, agg, plan, scale, group
+        self.peer = None
+        self.halo_kind = "none" if plan.world == 1 else "nccl"
+        if plan.world > 1 and halo in ("peer", "auto") and th.cuda.is_available() and dist.get_backend() == "nccl":
+            try:
+                self.peer = PeerHalo(plan, group)
+                self.halo_kind = "peer"
+            except Exception:
+                if halo == "peer":
+                    raise
 
     def forward(self, q, k, v, flows):
-        k_ext = halo_exchange(k, self.plan, self.group)
-        v_ext = halo_exchange(v, self.plan, self.group)
+        k_ext = halo_exchange(k, self.plan, self.group, self.peer, "k")
+        v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
         dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
         sign = -1.0 if self.search.dist_type == "l2" else 1.0
         weights = th.softmax(sign * self.scale * dists, -1)

@@ -1,0 +1,69 @@
+"""GPU, >= 2 devices: the frame-sharded path (NCCL and NVLink peer-memory halo exchange) must reproduce
+the single-GPU result -- outputs, indices and all gradients.  Spawns one process per GPU."""
+import os
+import sys
+
+import pytest
+import torch as th
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, halo, port, ret):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    import stnls_b200
+    from stnls_b200 import parallel
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    th.cuda.set_device(rank)
+    dev = th.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    B, T, F, H, W, HD, ws, wt, ps, K = 1, 9, 8, 24, 20, 2, 3, 2, 3, 6
+    g = th.Generator().manual_seed(5)
+    q, k, v = [th.randn(B, T, F, H, W, generator=g) for _ in range(3)]
+    flows = th.rand(B, 1, T, 2 * wt, 2, H, W, generator=g) / 2 + th.randint(-2, 3, (B, 1, T, 2 * wt, 2, H, W), generator=g) + 0.2
+    gout = th.randn(B, HD, T, F // HD, H, W, generator=g)
+
+    def run(plan, halo_kind, sl):
+        search = stnls_b200.search.NonLocalSearch(ws, wt, ps, K, nheads=HD, stride1=0.5, dist_type="l2",
+                                                  self_action="anchor", itype="float")
+        agg = stnls_b200.agg.WeightedPatchSum(ps=ps, stride0=1, itype="float")
+        model = parallel.ShardedSearchAgg(search, agg, plan, scale=10.0, halo=halo_kind)
+        ins = [x[:, sl].to(dev).requires_grad_(True) for x in (q, k, v)]
+        fl = flows[:, :, sl].to(dev).requires_grad_(True)
+        out, dists, inds = model(*ins, fl)
+        (out * gout[:, :, sl].to(dev)).sum().backward()
+        return [out.detach(), dists.detach(), inds.detach()] + [x.grad for x in ins] + [fl.grad], model.halo_kind
+
+    plan = parallel.ShardPlan(T, wt, world, rank)
+    got, kind = run(plan, halo, slice(plan.a, plan.b))
+    assert kind == halo, f"halo path {kind} != requested {halo}"
+    full, _ = run(parallel.ShardPlan(T, wt, 1, 0), "nccl", slice(0, T))
+    names = ["out", "dists", "inds", "grad_q", "grad_k", "grad_v", "grad_flows"]
+    errs = {}
+    for n, a, b in zip(names, got, full):
+        td = 1 if n in ("grad_q", "grad_k", "grad_v") else 2
+        b = b.narrow(td, plan.a, plan.b - plan.a)
+        errs[n] = float((a - b).abs().max())
+    ret[rank] = errs
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("halo", ["nccl", "peer"])
+def test_sharded_matches_single(halo):
+    if th.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import torch.multiprocessing as mp
+    world = 2
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    port = 29600 + (os.getpid() % 300) + (1 if halo == "peer" else 0)
+    mp.spawn(_worker, args=(world, halo, port, ret), nprocs=world, join=True)
+    assert len(ret) == world
+    for rank, errs in ret.items():
+        for n, e in errs.items():
+            tol = 0 if n == "inds" else 2e-3
+            assert e <= tol, f"rank {rank} {halo}: {n} differs by {e}"
