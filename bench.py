@@ -36,8 +36,11 @@ WORKLOADS = {
     # RVRT-style (configs[2], C3)
     "c3": dict(B=2, T=16, F=64, H=256, W=256, HD=4, ws=9, wt=1, ps=1, K=9, stride0=1, stride1=1.0,
                dist_type="prod", self_action=None, itype="float", scale=10.0),
+    # quarter-resolution stand-in for c4 (tuning runs)
+    "c4s": dict(B=1, T=7, F=64, H=540, W=960, HD=4, ws=9, wt=3, ps=3, K=20, stride0=1, stride1=1.0,
+                dist_type="prod", self_action=None, itype="float", scale=10.0),
     # 1080p slice per rank (configs[3], C4): T frames PER RANK
-    "c4": dict(B=1, T=4, F=64, H=1080, W=1920, HD=4, ws=9, wt=3, ps=3, K=20, stride0=1, stride1=1.0,
+    "c4": dict(B=1, T=7, F=64, H=1080, W=1920, HD=4, ws=9, wt=3, ps=3, K=20, stride0=1, stride1=1.0,
                dist_type="prod", self_action=None, itype="float", scale=10.0),
 }
 
@@ -46,7 +49,8 @@ def describe(wl, name, world):
     c = dict(wl)
     c["workload"] = {"c2": "README example (BASELINE configs[1]): search+agg fwd+bwd",
                      "c3": "RVRT-style GDA replacement (BASELINE configs[2])",
-                     "c4": "1080p slice (BASELINE configs[3])"}[name]
+                     "c4": "1080p slice (BASELINE configs[3])",
+                     "c4s": "1080p config at quarter resolution (tuning stand-in)"}[name]
     c["name"] = name
     c["T_global"] = wl["T"] * world
     c["sharding"] = "single GPU" if world == 1 else f"T sharded over {world} ranks, NCCL halo exchange of k,v"

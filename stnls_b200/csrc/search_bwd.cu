@@ -31,20 +31,23 @@ struct BwdParams {
   const uint8_t* reflect;
   stnls_geom g;
   stnls_search_opts o;
-  int K, mode, nquad, W_t, fast3;
+  int K, mode, nquad, W_t, fast3, ksplit;
   int64_t nthreads;
 };
 
 // MODE 0: int ; 1: bilinear ; 2: bilinear + flow grads (NLS layout) ; 3: same, refine layout
 // PS > 0: compile-time patch size (grad_q of the patch is kept in registers over the K neighbours)
-template <int MODE, int DIST, int PS, bool FAST>
-__global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __grid_constant__ BwdParams P) {
+// KSPLIT: one thread per (query, neighbour, quad) instead of a loop over the K neighbours
+template <int MODE, int DIST, int PS, bool FAST, bool KSPLIT>
+__global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : 4) search_bwd_kernel(const __grid_constant__ BwdParams P) {
   const stnls_geom& g = P.g;
   const stnls_search_opts& o = P.o;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P.nthreads) return;
   const int c4 = (int)(idx % P.nquad) * 4;
   int64_t wq = idx / P.nquad;
+  int k_lo = 0, k_hi = P.K;
+  if (KSPLIT) { k_lo = (int)(wq % P.K); k_hi = k_lo + 1; wq /= P.K; }
   int64_t r = wq;
   const int nw = (int)(r % g.nW); r /= g.nW;
   const int nh = (int)(r % g.nH); r /= g.nH;
@@ -63,12 +66,15 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
   const float* kb = P.k + (int64_t)n * g.Tk * kfs + c4;
   float* gkb = P.gk + (int64_t)n * g.Tk * kfs + c4;
 
-  float4 acc[(PS > 0) ? PS * PS : 1];
+  // grad_q of the query patch: kept in registers over the K neighbours (loop form) or sent straight
+  // to memory (KSPLIT: one neighbour per thread)
+  constexpr bool ACCQ = (PS > 0) && !KSPLIT;
+  float4 acc[ACCQ ? PS * PS : 1];
 #pragma unroll
-  for (int i = 0; i < ((PS > 0) ? PS * PS : 1); i++) acc[i] = f4zero();
+  for (int i = 0; i < (ACCQ ? PS * PS : 1); i++) acc[i] = f4zero();
 
   if (MODE == 0) {  // nls_int.cu:88-167
-    for (int ki = 0; ki < P.K; ki++) {
+    for (int ki = k_lo; ki < k_hi; ki++) {
       const int64_t oi = wq * P.K + ki;
       const float weight = P.gd[oi];
       const int* ind = reinterpret_cast<const int*>(P.inds) + oi * 3;
@@ -97,7 +103,7 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
             a0 = make_float4(w2 * (x0.x - x1.x), w2 * (x0.y - x1.y), w2 * (x0.z - x1.z), w2 * (x0.w - x1.w));
             a1 = make_float4(-a0.x, -a0.y, -a0.z, -a0.w);
           }
-          if (PS > 0) { float4& A = acc[pi * PS + pj]; A.x += a0.x; A.y += a0.y; A.z += a0.z; A.w += a0.w; }
+          if (ACCQ) { float4& A = acc[ACCQ ? pi * PS + pj : 0]; A.x += a0.x; A.y += a0.y; A.z += a0.z; A.w += a0.w; }
           else red_add4(gqf + qo, a0);
           red_add4(gkf + ko, a1);
         }
@@ -198,7 +204,7 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
             a0 = make_float4(w2 * (x0.x - x1.x), w2 * (x0.y - x1.y), w2 * (x0.z - x1.z), w2 * (x0.w - x1.w));
             a1 = make_float4(-a0.x, -a0.y, -a0.z, -a0.w);
           }
-          if (PS > 0) { float4& A = acc[pi * PS + pj]; A.x += a0.x; A.y += a0.y; A.z += a0.z; A.w += a0.w; }
+          if (ACCQ) { float4& A = acc[ACCQ ? pi * PS + pj : 0]; A.x += a0.x; A.y += a0.y; A.z += a0.z; A.w += a0.w; }
           else red_add4(gqf + qo, a0);
 #pragma unroll
           for (int ix = 0; ix < 2; ix++) {
@@ -229,13 +235,13 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
     const bool fast3 = FAST && (PS == 3) && P.fast3 && (P.K <= 32) && (o.off_Hq == 0) && (o.off_Wq == 0) &&
                        (rh + po >= 0) && (rh + po + 2 <= g.qH - 1) && (rw + po >= 0) && (rw + po + 2 <= g.qW - 1);
     if (!fast3) {
-      for (int ki = 0; ki < P.K; ki++) {
+      for (int ki = k_lo; ki < k_hi; ki++) {
         const Pre z = preamble(ki, true);
         if (z.valid) generic(z);
       }
     } else {
       unsigned slow = 0;
-      for (int ki = 0; ki < P.K; ki++) {
+      for (int ki = k_lo; ki < k_hi; ki++) {
         const Pre z = preamble(ki, true);
         if (!z.valid) continue;
         const int h0 = __float2int_rz(z.pph + (float)po), w0 = __float2int_rz(z.ppw + (float)po);
@@ -267,7 +273,8 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
           for (int j = 0; j < 4; j++) { B[j] = ldg4(vr + (pi + 1) * rs + j * g.Fp); accB[j] = f4zero(); }
 #pragma unroll
           for (int pj = 0; pj < 3; pj++) {
-            const float4 x0 = ldg4(qf + ((int64_t)(rh + pi + po) * g.qW + (rw + pj + po)) * g.Fp);
+            const int64_t qo = ((int64_t)(rh + pi + po) * g.qW + (rw + pj + po)) * g.Fp;
+            const float4 x0 = ldg4(qf + qo);
             const float w00 = gh[pi][0] * gw[pj][0], w01 = gh[pi][0] * gw[pj][1];
             const float w10 = gh[pi][1] * gw[pj][0], w11 = gh[pi][1] * gw[pj][1];
             float4 x1 = f4zero();
@@ -279,7 +286,8 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
               a0 = make_float4(w2 * (x0.x - x1.x), w2 * (x0.y - x1.y), w2 * (x0.z - x1.z), w2 * (x0.w - x1.w));
               a1 = make_float4(-a0.x, -a0.y, -a0.z, -a0.w);
             }
-            { float4& Aq = acc[(PS == 3) ? pi * 3 + pj : 0]; Aq.x += a0.x; Aq.y += a0.y; Aq.z += a0.z; Aq.w += a0.w; }
+            if (ACCQ) { float4& Aq = acc[ACCQ ? pi * 3 + pj : 0]; Aq.x += a0.x; Aq.y += a0.y; Aq.z += a0.z; Aq.w += a0.w; }
+            else red_add4(gqf + qo, a0);
             fma4(accA[pj], w00, a1); fma4(accA[pj + 1], w01, a1);
             fma4(accB[pj], w10, a1); fma4(accB[pj + 1], w11, a1);
             if (MODE >= 2) {  // update_dFlows, shared_kernel.cu:916-964 (all signs +1 in the interior)
@@ -305,7 +313,7 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
     }
   }
 
-  if (PS > 0) {
+  if (ACCQ) {
 #pragma unroll
     for (int pi = 0; pi < PS; pi++) {
       int r1 = rh + o.off_Hq + o.dilation * (pi + o.patch_offset);
@@ -316,21 +324,26 @@ __global__ void __launch_bounds__(128, FAST ? 3 : 4) search_bwd_kernel(const __g
         int r2 = rw + o.off_Wq + o.dilation * (pj + o.patch_offset);
         if (o.reflect_bounds) r2 = bnd(r2, g.qW);
         if (!inb(r2, g.qW)) continue;
-        red_add4(gqf + ((int64_t)r1 * g.qW + r2) * g.Fp, acc[pi * PS + pj]);
+        red_add4(gqf + ((int64_t)r1 * g.qW + r2) * g.Fp, acc[ACCQ ? pi * PS + pj : 0]);
       }
     }
   }
 }
 
 
-template <int MODE, int DIST>
-void launch_bwd(const BwdParams& P, cudaStream_t st) {
+template <int MODE, int DIST, bool KSPLIT>
+void launch_bwd_k(const BwdParams& P, cudaStream_t st) {
   const int tpb = 128;
   unsigned blocks = (unsigned)((P.nthreads + tpb - 1) / tpb);
-  if (P.o.ps == 1) search_bwd_kernel<MODE, DIST, 1, false><<<blocks, tpb, 0, st>>>(P);
-  else if (P.o.ps == 3 && P.fast3 && MODE != 0) search_bwd_kernel<MODE, DIST, 3, true><<<blocks, tpb, 0, st>>>(P);
-  else if (P.o.ps == 3) search_bwd_kernel<MODE, DIST, 3, false><<<blocks, tpb, 0, st>>>(P);
-  else search_bwd_kernel<MODE, DIST, 0, false><<<blocks, tpb, 0, st>>>(P);
+  if (P.o.ps == 1) search_bwd_kernel<MODE, DIST, 1, false, KSPLIT><<<blocks, tpb, 0, st>>>(P);
+  else if (P.o.ps == 3 && P.fast3 && MODE != 0) search_bwd_kernel<MODE, DIST, 3, true, KSPLIT><<<blocks, tpb, 0, st>>>(P);
+  else if (P.o.ps == 3) search_bwd_kernel<MODE, DIST, 3, false, KSPLIT><<<blocks, tpb, 0, st>>>(P);
+  else search_bwd_kernel<MODE, DIST, 0, false, KSPLIT><<<blocks, tpb, 0, st>>>(P);
+}
+template <int MODE, int DIST>
+void launch_bwd(const BwdParams& P, cudaStream_t st) {
+  if (P.ksplit) launch_bwd_k<MODE, DIST, true>(P, st);
+  else launch_bwd_k<MODE, DIST, false>(P, st);
 }
 
 }  // namespace
@@ -347,7 +360,7 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   P.gq = gq_cl; P.gk = gk_cl; P.gflows = grad_flows; P.q = q_cl; P.k = k_cl; P.flows = flows;
   P.gd = grad_dists; P.gi = grad_inds; P.inds = inds; P.kselect = kselect; P.reflect = reflect;
   P.g = *g; P.o = *o; P.K = K; P.nquad = g->Fp / 4; P.W_t = 2 * o->wt + 1;
-  P.fast3 = (o->ps == 3 && o->dilation == 1 && getenv("STNLS_BWD_FAST3")) ? 1 : 0;  // opt-in: measured slower
+  P.fast3 = (o->ps == 3 && o->dilation == 1 && !getenv("STNLS_NO_FAST3")) ? 1 : 0;
   const bool refine = o->wr > 0;
   if (o->itype_int) P.mode = 0;
   else if (!grad_flows) P.mode = 1;
@@ -357,6 +370,13 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   if (P.mode == 3) STNLS_REQUIRE(kselect && reflect, "search_backward: kselect/reflect required for refine flow grads");
   P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->nH * g->nW * P.nquad;
   if (P.nthreads == 0 || K == 0) return STNLS_OK;
+  // float modes, small launches: one thread per (query, neighbour, quad)
+  // measured on B200 (profiles/README.md): with ps=3 the split form wins while the whole problem is a few
+  // waves (C2: 0.65 -> 0.53 ms) and loses once the launch is large (1080p/4: 91 ms loop vs 132 ms split)
+  const char* env_ks = getenv("STNLS_SB_KSPLIT");
+  P.ksplit = (P.mode != 0 && o->ps >= 2 && P.nthreads < (1 << 20)) ? 1 : 0;
+  if (env_ks) P.ksplit = (env_ks[0] == '1' && P.mode != 0) ? 1 : 0;
+  if (P.ksplit) P.nthreads *= K;
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "search_backward: too many threads for one launch");
   cudaStream_t st = (cudaStream_t)stream;
   switch (P.mode * 2 + (o->dist_type ? 1 : 0)) {

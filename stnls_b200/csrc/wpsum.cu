@@ -100,7 +100,9 @@ __device__ __forceinline__ void axpy4(float4& y, float a, const float4 x) {
 // FAST3: ps == 3 && dilation == 1.  The 9 bilinear reads of one neighbour patch then share a 4x4
 // pixel footprint (all patch pixels have the same fractional position), so an interior (query, k)
 // pair reads 16 value pixels and issues 16 vector REDs instead of 36 + 36.
-template <bool INT, bool FAST3>
+// KSPLIT: one thread per (query, neighbour, quad) instead of a loop over the K neighbours -- K times
+// more threads in flight for a kernel that is latency-bound, not bandwidth-bound
+template <bool INT, bool FAST3, bool KSPLIT>
 __global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant__ AggParams P) {
   const stnls_geom& g = P.g;
   const stnls_agg_opts& o = P.o;
@@ -108,7 +110,9 @@ __global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P.nthreads) return;
   const int c4 = (int)(idx % P.nquad) * 4;
-  const int64_t wq = idx / P.nquad;
+  int64_t wq = idx / P.nquad;
+  int k_lo = 0, k_hi = o.K;
+  if (KSPLIT) { k_lo = (int)(wq % o.K); k_hi = k_lo + 1; wq /= o.K; }
   int64_t r = wq;
   const int nw = (int)(r % g.nW); r /= g.nW;
   const int nh = (int)(r % g.nH); r /= g.nH;
@@ -212,7 +216,7 @@ __global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant
   };
 
   if (!FAST3) {
-    for (int ki = 0; ki < o.K; ki++) generic(ki);
+    for (int ki = k_lo; ki < k_hi; ki++) generic(ki);
     return;
   }
 
@@ -221,7 +225,7 @@ __global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant
   const int po = o.patch_offset;
   const bool refok = (rh + po >= 0) && (rh + po + 2 <= H - 1) && (rw + po >= 0) && (rw + po + 2 <= W - 1);
   if (!refok || o.K > 32) {
-    for (int ki = 0; ki < o.K; ki++) generic(ki);
+    for (int ki = k_lo; ki < k_hi; ki++) generic(ki);
     return;
   }
   float4 grp[9];  // the query's own 3x3 patch of grad_out, read once for all K neighbours
@@ -230,7 +234,7 @@ __global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant
 #pragma unroll
     for (int pj = 0; pj < 3; pj++) grp[pi * 3 + pj] = ldg4(gof + ((int64_t)(rh + pi + po) * W + (rw + pj + po)) * g.Fp);
   unsigned slow = 0;
-  for (int ki = 0; ki < o.K; ki++) {
+  for (int ki = k_lo; ki < k_hi; ki++) {
     const int64_t oi = wq * o.K + ki;
     const float* f = reinterpret_cast<const float*>(P.flows) + oi * 3;
     float n0 = (float)t + f[0], c1 = (float)rh + f[1], c2 = (float)rw + f[2];
@@ -339,9 +343,22 @@ extern "C" int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* gr
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
   cudaStream_t st = (cudaStream_t)stream;
   const bool fast3 = (o->ps == 3 && o->dilation == 1 && !getenv("STNLS_NO_FAST3"));
-  if (o->itype_int) wpsum_bwd_kernel<true, false><<<blocks, 128, 0, st>>>(P);
-  else if (fast3) wpsum_bwd_kernel<false, true><<<blocks, 128, 0, st>>>(P);
-  else wpsum_bwd_kernel<false, false><<<blocks, 128, 0, st>>>(P);
+  const bool ksplit = o->ps >= 2 && getenv("STNLS_WPB_NO_KSPLIT") == nullptr;  // default on: 0.47 -> 0.29 ms on C2
+  if (ksplit) {
+    P.nthreads *= o->K;
+    STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_backward: too many threads for one launch");
+    blocks = (unsigned)((P.nthreads + 127) / 128);
+  }
+  if (o->itype_int) {
+    if (ksplit) wpsum_bwd_kernel<true, false, true><<<blocks, 128, 0, st>>>(P);
+    else wpsum_bwd_kernel<true, false, false><<<blocks, 128, 0, st>>>(P);
+  } else if (fast3) {
+    if (ksplit) wpsum_bwd_kernel<false, true, true><<<blocks, 128, 0, st>>>(P);
+    else wpsum_bwd_kernel<false, true, false><<<blocks, 128, 0, st>>>(P);
+  } else {
+    if (ksplit) wpsum_bwd_kernel<false, false, true><<<blocks, 128, 0, st>>>(P);
+    else wpsum_bwd_kernel<false, false, false><<<blocks, 128, 0, st>>>(P);
+  }
   STNLS_CHECK_LAUNCH("wpsum_backward");
   return STNLS_OK;
 }
