@@ -183,6 +183,16 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def load_traffic(workload, kernel):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture (profiles/traffic.json)."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get(workload, {}).get(kernel)
+    except OSError:
+        return None
+
+
 def run_product(args):
     import torch.distributed as dist
     import stnls_b200
@@ -394,7 +404,8 @@ def main():
     dur_s = kt[dom]["ms_per_launch"] * 1e-3
     achieved = alg[dom]["bytes"] / dur_s / 1e9
     roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak,
+                "traffic": load_traffic(args.workload, dom) if world == 1 else None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg[dom]["bytes"], "ms_per_launch": kt[dom]["ms_per_launch"],
                 "share_of_step": kt[dom]["ms_per_step"] / ms_per_step}
     clocks = r["clocks"]
