@@ -196,6 +196,7 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
   C.n1 = o.itype_int ? (int)o.stride1 : (int)(o.stride1 * D);
   C.n2 = o.dilation * D;
   C.u = 1.f / D;
+  C.D = D;
   if (C.n1 < 1 || C.n2 < 1) return false;
   C.M = (wsz - 1) * C.n1 + (ps - 1) * C.n2 + 1;
   if (C.M > 32) return false;

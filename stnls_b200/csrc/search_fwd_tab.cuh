@@ -19,6 +19,7 @@ struct TabCfg {
   int q_off, ax_off, msk_off, key_off, warp_f4;  // per-warp smem carve, float4 units
   int wpb;        // warps per block
   float inv_G, inv_wsz, inv_Q4, inv_M;
+  int D;          // lattice denominator (u = 1/D)
 };
 
 // one per translation unit; each picks dist_type / ps / channel-quad template variants at run time

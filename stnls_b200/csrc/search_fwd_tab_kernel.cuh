@@ -64,14 +64,18 @@ __device__ __forceinline__ void fma4(float4& v, float w, const float4 t) {
 // (shared_kernel.cu:738-771; tap order (0,0),(0,1),(1,0),(1,1) and weight gh*gw as in the reference)
 template <bool INT>
 __device__ __forceinline__ float4 lattice_value(const char* kc, const float4 eh, const float4 ew) {
-  const int oh0 = __float_as_int(eh.x), ow0 = __float_as_int(ew.x);   // byte offsets, < 0: tap outside
+  const int oh0 = __float_as_int(eh.x), ow0 = __float_as_int(ew.x);   // byte offsets (always inside the frame)
   if (INT) return ldg4b(kc, (unsigned)(oh0 + ow0));
   const int oh1 = __float_as_int(eh.y), ow1 = __float_as_int(ew.y);
+  // a tap outside the frame carries weight 0 and a legal offset (axis tables), so no tap branches:
+  // fma(0, finite, v) == v, i.e. the same value the reference gets by dropping the tap
+  const float4 t00 = ldg4b(kc, (unsigned)(oh0 + ow0)), t01 = ldg4b(kc, (unsigned)(oh0 + ow1));
+  const float4 t10 = ldg4b(kc, (unsigned)(oh1 + ow0)), t11 = ldg4b(kc, (unsigned)(oh1 + ow1));
   float4 v = f4zero();
-  if ((oh0 | ow0) >= 0) fma4(v, eh.z * ew.z, ldg4b(kc, (unsigned)(oh0 + ow0)));
-  if ((oh0 | ow1) >= 0) fma4(v, eh.z * ew.w, ldg4b(kc, (unsigned)(oh0 + ow1)));
-  if ((oh1 | ow0) >= 0) fma4(v, eh.w * ew.z, ldg4b(kc, (unsigned)(oh1 + ow0)));
-  if ((oh1 | ow1) >= 0) fma4(v, eh.w * ew.w, ldg4b(kc, (unsigned)(oh1 + ow1)));
+  fma4(v, eh.z * ew.z, t00);
+  fma4(v, eh.z * ew.w, t01);
+  fma4(v, eh.w * ew.z, t10);
+  fma4(v, eh.w * ew.w, t11);
   return v;
 }
 
@@ -156,6 +160,10 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
   }
   const bool qfull = qmask == ((ps2 >= 32) ? 0xffffffffu : ((1u << ps2) - 1u));
 
+  // window description of the first 32 groups, lane = group: computed once, handed out by shuffles
+  const Group<CC> all32 = group_params<INT, REFINE>(P, c, min(lane, P.nG - 1));
+  const bool one_chunk = P.nG <= 32;
+
   // -- pass 1 (NLS anchor): candidate whose offset is (0,0,0) / nearest to it (anchor_self_kernel.cu:62-89)
   int a_nls = 0;
   if (anchored && !REFINE) {
@@ -165,7 +173,8 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
     const int nchunks = (P.nG + 31) / 32;
     for (int ch = 0; ch < nchunks; ch++) {
       int gi = ch * 32 + lane;
-      Group<CC> mine = group_params<INT, REFINE>(P, c, min(gi, P.nG - 1));
+      Group<CC> mine = all32;
+      if (ch > 0) mine = group_params<INT, REFINE>(P, c, min(gi, P.nG - 1));
       int pend = min(P.L, (ch + 1) * 32 * P.G);
       for (int base = ch * 32 * P.G; base < pend; base += 32) {
         int pos = min(base + lane, pend - 1);
@@ -200,7 +209,9 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
   const int rowsc = g.kW * g.Fp * 4;  // bytes per key row
   for (int g0 = 0; g0 < P.nG; g0 += C.nb) {
     const int nbg = min(C.nb, P.nG - g0);
-    Group<CC> mine = group_params<INT, REFINE>(P, c, g0 + min(lane, nbg - 1));
+    Group<CC> mine;
+    if (one_chunk) mine = shfl_group(all32, g0 + min(lane, nbg - 1));
+    else mine = group_params<INT, REFINE>(P, c, g0 + min(lane, nbg - 1));
     int my_ag = 0;
     if (REFINE && anchored) my_ag = refine_group_anchor<CC>(P, c, mine, g0 + min(lane, nbg - 1));
     if (lane < nbg) sts1(sb + (gfrb + lane) * 4, (unsigned)((mine.ok && inb(mine.t, g.T)) ? (mine.t - g.tk0) : -1));
@@ -221,17 +232,20 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
           int p = (int)a - (int)s1c * (int)off + o.dilation * o.patch_offset + m;
           if (o.reflect_bounds) p = bnd(p, lim);
           pv = inb(p, lim);
-          o0 = pv ? p * sc : -1;
+          o0 = pv ? p * sc : 0;  // invalid lattice points are filled from a legal address and never read
         } else {
           float basep = fmaf(-(float)s1c, (float)off, (float)a) + (float)(o.dilation * o.patch_offset);
           float p = fmaf(C.u, (float)m, basep);
           if (o.reflect_bounds) p = bnd(p, lim);
           pv = inb(p, lim);
           int t0 = __float2int_rz(p), t1 = __float2int_rz(p + 1);
-          w0 = fmaxf(0.f, 1 - fabsf(t0 - p));
-          w1 = fmaxf(0.f, 1 - fabsf(t1 - p));
-          o0 = inb(t0, lim) ? t0 * sc : -1;
-          o1 = inb(t1, lim) ? t1 * sc : -1;
+          // a tap outside the frame is dropped by the reference (shared_kernel.cu:752-756): here its
+          // weight becomes 0 and its offset a legal one, so the lattice loop below needs no tap branches
+          const bool v0 = inb(t0, lim), v1 = inb(t1, lim);
+          w0 = v0 ? fmaxf(0.f, 1 - fabsf(t0 - p)) : 0.f;
+          w1 = v1 ? fmaxf(0.f, 1 - fabsf(t1 - p)) : 0.f;
+          o0 = v0 ? t0 * sc : 0;
+          o1 = v1 ? t1 * sc : (v0 ? t0 * sc : 0);
         }
         sts4(sb + (axb + (gl * 2 + axis) * M + m) * 16, make_float4(__int_as_float(o0), __int_as_float(o1), w0, w1));
       }
@@ -247,7 +261,6 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
     for (int gl = 0; gl < nbg; gl++) {
       const int fr = (int)lds1(sb + (gfrb + gl) * 4);
       if (fr < 0) continue;
-      const unsigned mh_ok = lds1(sb + (mskb + gl * 2) * 4), mw_ok = lds1(sb + (mskb + gl * 2 + 1) * 4);
       const unsigned Ah = sb + (axb + (gl * 2) * M) * 16, Aw = Ah + M * 16;
       const int Tg = Tb + gl * C.GS4;
       const char* kf = reinterpret_cast<const char*>(kbase + (int64_t)fr * kfs);
@@ -257,20 +270,20 @@ __global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_con
         asm volatile("" : "+l"(kc));  // keep the frame pointer in registers (no re-derivation per tap)
         const unsigned Tgc = sb + (Tg + c4 * C.PS4) * 16;
         const unsigned Mp16 = C.Mp * 16;
+#pragma unroll 2
         for (int x = lane / Q4T; x < MM; x += 32 / Q4T) {
           const unsigned d = ldsh(sb + x * 2);
           const unsigned mh = d >> 8, mw = d & 255;
-          if (!(((mh_ok >> mh) & (mw_ok >> mw)) & 1)) continue;
           sts4(Tgc + mh * Mp16 + mw * 16, lattice_value<INT>(kc, lds4(Ah + mh * 16), lds4(Aw + mw * 16)));
         }
       } else {
+#pragma unroll 2
         for (int it = lane; it < MM * Q4; it += 32) {
           int x, c4;
           if (C.q4sh >= 0) { x = it >> C.q4sh; c4 = it & (Q4 - 1); }
           else { x = fdiv(it, C.inv_Q4); c4 = it - x * Q4; }
           const unsigned d = ldsh(sb + x * 2);
           const unsigned mh = d >> 8, mw = d & 255;
-          if (!(((mh_ok >> mh) & (mw_ok >> mw)) & 1)) continue;
           sts4(sb + (Tg + c4 * C.PS4 + mh * C.Mp + mw) * 16,
                lattice_value<INT>(kf + c4 * 16, lds4(Ah + mh * 16), lds4(Aw + mw * 16)));
         }
