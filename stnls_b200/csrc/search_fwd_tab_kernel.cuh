@@ -81,7 +81,7 @@ __device__ __forceinline__ float4 lattice_value(const char* kc, const float4 eh,
 
 // PS: patch size (0 = run time); Q4T: channel quads (0 = run time)
 template <bool INT, int DIST, bool REFINE, int PS, int Q4T>
-__global__ void __launch_bounds__(256, 3) search_fwd_tab_kernel(const __grid_constant__ FwdParams P,
+__global__ void __launch_bounds__(256, (PS * PS * Q4T >= 36 || Q4T == 0) ? 3 : 4) search_fwd_tab_kernel(const __grid_constant__ FwdParams P,
                                                                 const __grid_constant__ TabCfg C) {
   typedef typename CT<INT>::type CC;
   extern __shared__ float4 smem4[];
