@@ -133,6 +133,20 @@ int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* grad_flows,
                          const void* flows, const stnls_geom* g, const stnls_agg_opts* o,
                          stnls_stream_t stream);
 
+/* ---- NonLocalGather (K-stacked aggregation) ---------------------------------------
+ * replaces  gather_int_forward / gather_bilin2d_forward / gather_int_backward / gather_bilin2d_backward
+ *           (lib/csrc/agg/gather.cpp; kernels lib/csrc/agg/gather_{int,bilin2d}_kernel.cu, driven by
+ *           lib/stnls/agg/gather.py:70-276).  Same arguments as the weighted patch sum, but the sum over the
+ *           K neighbours is NOT taken: stack_cl / gstack_cl are (N*K, Tq, H, W, Fp), slab n*K + k holding
+ *           neighbour k -- the cl form of the reference's (B,HD,K,T,F,H,W) stack.                        */
+int stnls_gather_forward(float* stack_cl, const float* v_cl, const float* weights, const void* flows,
+                         const int* counts_h, const int* counts_w,
+                         const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream);
+int stnls_gather_backward(float* gv_cl, float* grad_weights, float* grad_flows,
+                          const float* gstack_cl, const float* v_cl, const float* weights,
+                          const void* flows, const stnls_geom* g, const stnls_agg_opts* o,
+                          stnls_stream_t stream);
+
 /* separable patch-overlap counts (host helper, no GPU): counts_h[h] = #{(nh,pi): nh*stride0 +
  * dilation*(pi+patch_offset) == h}; equals what gather_add_forward_kernel counts atomically
  * (lib/csrc/agg/gather_add_kernel.cu:94-97).  Returns the minimum count (0 => reference asserts). */

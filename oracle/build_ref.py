@@ -8,7 +8,8 @@ into oracle/_ref/stnls_cuda_ref*.so so the GPU box can run the reference itself 
   `.type()` -> `.scalar_type()` (torch 2.11 dropped the implicit DeprecatedTypeProperties ->
   ScalarType conversion).
 * Only the hot-path files are built: search/non_local_search*, search/refinement*, agg/gather_add*,
-  nn/anchor_self* (+ headers shared_kernel.cu, nls_int.cu, nls_bilin2d.cu) and a 10-line pybind file.
+  nn/anchor_self*, and the next rows nn/search_flow*, agg/gather{,_int,_bilin2d}* (+ their header-style .cu
+  includes) and a 10-line pybind file.
 * Output: oracle/_ref/ (git-ignored, NOT gpurun-ignored).  Run in this container (no GPU needed);
   /root/reference does not exist on the GPU box.
 """
@@ -29,8 +30,13 @@ FILES = ["shared_kernel.cu",
          "search/non_local_search_bilin2d_kernel.cu",
          "search/refinement.cpp", "search/refinement_int_kernel.cu", "search/refinement_bilin2d_kernel.cu",
          "agg/gather_add.cpp", "agg/gather_add_kernel.cu",
-         "nn/anchor_self.cpp", "nn/anchor_self_kernel.cu"]
-HEADER_ONLY = {"shared_kernel.cu", "search/nls_int.cu", "search/nls_bilin2d.cu"}
+         "nn/anchor_self.cpp", "nn/anchor_self_kernel.cu",
+         # next rows: N1 search_flow, N3 NonLocalGather
+         "nn/shared_flows.cu", "nn/search_flow.cpp", "nn/search_flow_kernel.cu",
+         "agg/gather_int.cu", "agg/gather_bilin2d.cu", "agg/gather.cpp",
+         "agg/gather_int_kernel.cu", "agg/gather_bilin2d_kernel.cu"]
+HEADER_ONLY = {"shared_kernel.cu", "search/nls_int.cu", "search/nls_bilin2d.cu", "nn/shared_flows.cu",
+               "agg/gather_int.cu", "agg/gather_bilin2d.cu"}
 
 PYBIND = """
 #include <torch/extension.h>
@@ -38,11 +44,15 @@ void init_non_local_search(py::module &);
 void init_refinement(py::module &);
 void init_anchor_self(py::module &);
 void init_gather_add(py::module &);
+void init_gather(py::module &);
+void init_search_flow(py::module &);
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   init_non_local_search(m);
   init_refinement(m);
   init_anchor_self(m);
   init_gather_add(m);
+  init_gather(m);
+  init_search_flow(m);
 }
 """
 

@@ -326,3 +326,43 @@ def gather_add_backward(grad_out, vid, weights, flows, counts, ps, stride0, dila
     if gf is not None:
         gf = gf.reshape(weights.shape + (3,))
     return gvid, gw, gf
+
+
+# ---------------------------------------------------------------------------------------------
+#   NonLocalGather (K-stacked aggregation)
+# ---------------------------------------------------------------------------------------------
+
+def gather_forward(vid, weights, inds, ps, stride0, dilation=1, reflect_bounds=True, use_adj=False,
+                   itype="float"):
+    """lib/stnls/agg/gather.py:79-160 ; returns (stack (B,HD,K,T,F,H,W), counts (H,W))"""
+    vid, w, f = _agg_prep(vid, weights, inds, itype)
+    B, HD, T, F, H, W = vid.shape
+    Q, K = w.shape[2:]
+    stack = th.zeros((B, HD, K, T, F, H, W), dtype=th.float32)
+    counts = th.zeros((H, W), dtype=th.int32)
+    patch_offset = 0 if use_adj else -(ps // 2)
+    lib().oracle_gather_forward(_p(stack), _p(counts), _p(vid), _p(w), _p(f), B, HD, T, F, H, W,
+                                Q, K, ps, stride0, dilation, int(reflect_bounds), patch_offset,
+                                int(itype == "int"))
+    assert th.all(counts > 0)
+    stack = stack / (counts.view(1, 1, 1, 1, 1, H, W) + 1e-10)
+    return stack, counts
+
+
+def gather_backward(grad_stack, vid, weights, inds, counts, ps, stride0, dilation=1, reflect_bounds=True,
+                    use_adj=False, itype="float"):
+    """lib/stnls/agg/gather.py:162-253 ; grad_stack (B,HD,K,T,F,H,W)"""
+    vid, w, f = _agg_prep(vid, weights, inds, itype)
+    B, HD, T, F, H, W = vid.shape
+    Q, K = w.shape[2:]
+    g = (grad_stack.float() / (counts.view(1, 1, 1, 1, 1, H, W) + 1e-10)).contiguous()
+    gvid, gw = th.zeros_like(vid), th.zeros_like(w)
+    gi = th.zeros(f.shape, dtype=th.float32) if itype != "int" else None
+    patch_offset = 0 if use_adj else -(ps // 2)
+    lib().oracle_gather_backward(_p(gvid), _p(gw), _p(gi), _p(g), _p(vid), _p(w), _p(f),
+                                 B, HD, T, F, H, W, Q, K, ps, stride0, dilation,
+                                 int(reflect_bounds), patch_offset, int(itype == "int"))
+    gw = gw.reshape(weights.shape)
+    if gi is not None:
+        gi = gi.reshape(weights.shape + (3,))
+    return gvid, gw, gi

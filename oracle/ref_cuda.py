@@ -203,3 +203,38 @@ def gather_add_backward(grad_out, vid, weights, flows, counts, ps, stride0, dila
                                           reflect_bounds, patch_offset)
         gf = gf.reshape(weights.shape + (3,))
     return gvid, gw.reshape(weights.shape), gf
+
+
+def gather_forward(vid, weights, inds, ps, stride0, dilation=1, reflect_bounds=True, use_adj=False, itype="float"):
+    """Drives gather_{int,bilin2d}_forward as lib/stnls/agg/gather.py:79-160 does."""
+    vid, w, f = cref._agg_prep(vid, weights, inds, itype)
+    B, HD, T, F, H, W = vid.shape
+    K = w.shape[-1]
+    stack = th.zeros((B, HD, K, T, F, H, W), device=vid.device, dtype=vid.dtype)
+    counts = th.zeros((B, HD, H, W), device=vid.device, dtype=th.int32)
+    patch_offset = 0 if use_adj else -(ps // 2)
+    fn = mod().gather_int_forward if itype == "int" else mod().gather_bilin2d_forward
+    fn(vid, w, f, stack, counts, ps, 1, dilation, stride0, reflect_bounds, patch_offset)
+    stack = stack / (counts.view(B, HD, 1, 1, 1, H, W) + 1e-10)
+    return stack, counts
+
+
+def gather_backward(grad_stack, vid, weights, inds, counts, ps, stride0, dilation=1, reflect_bounds=True,
+                    use_adj=False, itype="float"):
+    """Drives gather_{int,bilin2d}_backward as lib/stnls/agg/gather.py:162-253 does."""
+    vid, w, f = cref._agg_prep(vid, weights, inds, itype)
+    B, HD, T, F, H, W = vid.shape
+    g = (grad_stack.float() / (counts.view(B, HD, 1, 1, 1, H, W) + 1e-10)).contiguous()
+    gvid, gw = th.zeros_like(vid), th.zeros_like(w)
+    patch_offset = 0 if use_adj else -(ps // 2)
+    stack = th.zeros_like(g)  # saved forward output; the kernels do not read it
+    gi = None
+    if itype == "int":
+        mod().gather_int_backward(gvid, gw, g, vid, w, f, stack, counts, ps, 1, dilation, stride0,
+                                  reflect_bounds, patch_offset)
+    else:
+        gi = th.zeros(f.shape, dtype=th.float32, device=vid.device)
+        mod().gather_bilin2d_backward(gvid, gw, gi, g, vid, w, f, stack, counts, ps, 1, dilation, stride0,
+                                      reflect_bounds, patch_offset)
+        gi = gi.reshape(weights.shape + (3,))
+    return gvid, gw.reshape(weights.shape), gi

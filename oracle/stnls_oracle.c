@@ -801,3 +801,167 @@ void oracle_gather_add_backward(float* gvid, float* gweights, float* gflows,
     }
   }
 }
+
+/*
+ * NonLocalGather (K-stacked aggregation) forward.
+ *   int  : lib/csrc/agg/gather_int_kernel.cu:19-97   + lib/csrc/agg/gather_int.cu:15-94
+ *   float: lib/csrc/agg/gather_bilin2d_kernel.cu:24-98 + lib/csrc/agg/gather_bilin2d.cu:14-93
+ * vid (B,HD,T,F,H,W); weights (B,HD,Q,K); inds (B,HD,Q,K,3); stack (B,HD,K,T,F,H,W) pre-zeroed;
+ * counts (H,W) int32 pre-zeroed (the reference keeps one identical map per (b,hd)).  pt == 1.
+ */
+void oracle_gather_forward(float* stack, int* counts, const float* vid, const float* weights,
+                           const void* inds_v, int B, int HD, int T, int F, int H, int W,
+                           int Q, int K, int ps, int stride0, int dilation, int reflect_bounds,
+                           int patch_offset, int itype_int){
+  const int* inds_i = (const int*)inds_v; const float* inds_f = (const float*)inds_v;
+  int nW = (W-1)/stride0+1, nHW = nW*((H-1)/stride0+1);
+  int64_t vsz = (int64_t)T*F*H*W;
+  #pragma omp parallel for collapse(3) schedule(static)
+  for (int b=0; b<B; b++) for (int hd=0; hd<HD; hd++) for (int qi=0; qi<Q; qi++){
+    const float* v = vid + ((int64_t)b*HD+hd)*vsz;
+    int ref[3]; pixel_loc(ref,qi,stride0,nW,nHW,H,W);
+    for (int ki=0; ki<K; ki++){
+      int64_t fo = ((((int64_t)b*HD+hd)*Q+qi)*K+ki);
+      float weight = weights[fo];
+      float* o = stack + (((int64_t)b*HD+hd)*K+ki)*vsz;
+      int r0 = bounds_i(ref[0],T);
+      if (itype_int){
+        int nl0 = bounds_i(ref[0]+inds_i[fo*3],T), nl1 = bounds_i(ref[1]+inds_i[fo*3+1],H),
+            nl2 = bounds_i(ref[2]+inds_i[fo*3+2],W);
+        int n0 = bounds_i(nl0,T);
+        for (int pi=0; pi<ps; pi++) for (int pj=0; pj<ps; pj++){
+          int r1 = ref[1]+dilation*(pi+patch_offset), r2 = ref[2]+dilation*(pj+patch_offset);
+          int vref = inb_i(r0,T) && inb_i(r1,H) && inb_i(r2,W);
+          int n1 = nl1+dilation*(pi+patch_offset); if (reflect_bounds) n1 = bounds_i(n1,H);
+          int n2 = nl2+dilation*(pj+patch_offset); if (reflect_bounds) n2 = bounds_i(n2,W);
+          int vnl = inb_i(n0,T) && inb_i(n1,H) && inb_i(n2,W);
+          if (ki==0 && vref && r0==0 && b==0 && hd==0){
+            #pragma omp atomic
+            counts[r1*W+r2] += 1;
+          }
+          if (!(vref && vnl)) continue;
+          for (int c=0; c<F; c++){
+            float add = weight*v[(((int64_t)n0*F+c)*H+n1)*W+n2];
+            #pragma omp atomic
+            o[(((int64_t)r0*F+c)*H+r1)*W+r2] += add;
+          }
+        }
+      }else{
+        float nl0 = bounds_f(ref[0]+inds_f[fo*3],T), nl1 = bounds_f(ref[1]+inds_f[fo*3+1],H),
+              nl2 = bounds_f(ref[2]+inds_f[fo*3+2],W);
+        float n0 = bounds_f(nl0,T);
+        for (int pi=0; pi<ps; pi++) for (int pj=0; pj<ps; pj++){
+          int r1 = ref[1]+dilation*(pi+patch_offset), r2 = ref[2]+dilation*(pj+patch_offset);
+          int vref = inb_i(r0,T) && inb_i(r1,H) && inb_i(r2,W);
+          float n1 = nl1+(float)(dilation*(pi+patch_offset)); if (reflect_bounds) n1 = bounds_f(n1,H);
+          float n2 = nl2+(float)(dilation*(pj+patch_offset)); if (reflect_bounds) n2 = bounds_f(n2,W);
+          int vnl = inb_f(n0,T) && inb_f(n1,H) && inb_f(n2,W);
+          if (ki==0 && vref && r0==0 && b==0 && hd==0){
+            #pragma omp atomic
+            counts[r1*W+r2] += 1;
+          }
+          if (!(vref && vnl)) continue;
+          int ti = (int)lrintf(roundf(n0));
+          for (int c=0; c<F; c++){
+            float pix = bilin2d_interp(v + ((int64_t)ti*F+c)*H*W, n1, n2, H, W);
+            float add = weight*pix;
+            #pragma omp atomic
+            o[(((int64_t)r0*F+c)*H+r1)*W+r2] += add;
+          }
+        }
+      }
+    }
+  }
+}
+
+/*
+ * NonLocalGather backward.
+ *   int  : lib/csrc/agg/gather_int_kernel.cu:150-230    + lib/csrc/agg/gather_int.cu:98-174
+ *   float: lib/csrc/agg/gather_bilin2d_kernel.cu:160-250 + lib/csrc/agg/gather_bilin2d.cu:95-236
+ *          (taps outside the frame are REFLECTED here, :188-189, not dropped as in gather_add)
+ * gstack (B,HD,K,T,F,H,W) is the incoming gradient ALREADY divided by counts (gather.py:231).
+ */
+void oracle_gather_backward(float* gvid, float* gweights, float* ginds,
+                            const float* gstack, const float* vid, const float* weights,
+                            const void* inds_v, int B, int HD, int T, int F, int H, int W,
+                            int Q, int K, int ps, int stride0, int dilation, int reflect_bounds,
+                            int patch_offset, int itype_int){
+  const int* inds_i = (const int*)inds_v; const float* inds_f = (const float*)inds_v;
+  int nW = (W-1)/stride0+1, nHW = nW*((H-1)/stride0+1);
+  int64_t vsz = (int64_t)T*F*H*W;
+  #pragma omp parallel for collapse(3) schedule(static)
+  for (int b=0; b<B; b++) for (int hd=0; hd<HD; hd++) for (int qi=0; qi<Q; qi++){
+    const float* v = vid + ((int64_t)b*HD+hd)*vsz; float* gv = gvid + ((int64_t)b*HD+hd)*vsz;
+    int ref[3]; pixel_loc(ref,qi,stride0,nW,nHW,H,W);
+    int r0 = bounds_i(ref[0],T);
+    for (int ki=0; ki<K; ki++){
+      int64_t fo = ((((int64_t)b*HD+hd)*Q+qi)*K+ki);
+      float weight = weights[fo];
+      const float* go = gstack + (((int64_t)b*HD+hd)*K+ki)*vsz;
+      if (itype_int){
+        int nl0 = bounds_i(ref[0]+inds_i[fo*3],T), nl1 = bounds_i(ref[1]+inds_i[fo*3+1],H),
+            nl2 = bounds_i(ref[2]+inds_i[fo*3+2],W);
+        int n0 = bounds_i(nl0,T);
+        for (int pi=0; pi<ps; pi++) for (int pj=0; pj<ps; pj++){
+          int r1 = ref[1]+dilation*(pi+patch_offset), r2 = ref[2]+dilation*(pj+patch_offset);
+          int n1 = nl1+dilation*(pi+patch_offset); if (reflect_bounds) n1 = bounds_i(n1,H);
+          int n2 = nl2+dilation*(pj+patch_offset); if (reflect_bounds) n2 = bounds_i(n2,W);
+          if (!(inb_i(r0,T) && inb_i(r1,H) && inb_i(r2,W))) continue;
+          if (!(inb_i(n0,T) && inb_i(n1,H) && inb_i(n2,W))) continue;
+          float acc = 0;
+          for (int c=0; c<F; c++){
+            float g = go[(((int64_t)r0*F+c)*H+r1)*W+r2];
+            int64_t iv = (((int64_t)n0*F+c)*H+n1)*W+n2;
+            float add = g*weight;
+            #pragma omp atomic
+            gv[iv] += add;
+            acc += g*v[iv];
+          }
+          gweights[fo] += acc;
+        }
+      }else{
+        float c0 = bounds_f(ref[0]+inds_f[fo*3],T);
+        float c1 = ref[1]+inds_f[fo*3+1], c2 = ref[2]+inds_f[fo*3+2];
+        int signH = inb_f(c1,H) ? 1 : -1; c1 = bounds_f(c1,H);
+        int signW = inb_f(c2,W) ? 1 : -1; c2 = bounds_f(c2,W);
+        float n0 = bounds_f(c0,T);
+        for (int pi=0; pi<ps; pi++) for (int pj=0; pj<ps; pj++){
+          int r1 = ref[1]+dilation*(pi+patch_offset), r2 = ref[2]+dilation*(pj+patch_offset);
+          float n1 = c1+(float)(dilation*(pi+patch_offset));
+          int sH = inb_f(n1,H) ? 1 : -1; if (reflect_bounds) n1 = bounds_f(n1,H);
+          float n2 = c2+(float)(dilation*(pj+patch_offset));
+          int sW = inb_f(n2,W) ? 1 : -1; if (reflect_bounds) n2 = bounds_f(n2,W);
+          if (!(inb_i(r0,T) && inb_i(r1,H) && inb_i(r2,W))) continue;
+          if (!(inb_f(n0,T) && inb_f(n1,H) && inb_f(n2,W))) continue;
+          int ti = (int)lrintf(roundf(n0));
+          float acc=0, iW=0, iH=0;
+          for (int c=0; c<F; c++){
+            float g = go[(((int64_t)r0*F+c)*H+r1)*W+r2];
+            float wg = g*weight, pix=0, igW=0, igH=0;
+            const float* plane = v + ((int64_t)ti*F+c)*H*W;
+            float* gplane = gv + ((int64_t)ti*F+c)*H*W;
+            for (int ix=0; ix<2; ix++) for (int jx=0; jx<2; jx++){
+              int h_i = (int)truncf(n1+ix), w_i = (int)truncf(n2+jx);
+              float gH = fmaxf(0.f,1-fabsf(n1-h_i)), gW = fmaxf(0.f,1-fabsf(n2-w_i));
+              float w = gH*gW;
+              h_i = bounds_i(h_i,H); w_i = bounds_i(w_i,W);
+              float vp = plane[(int64_t)h_i*W+w_i];
+              pix += w*vp;
+              igW += (jx==0) ? -gH*vp : gH*vp;
+              igH += (ix==0) ? -gW*vp : gW*vp;
+              float add = w*wg;
+              #pragma omp atomic
+              gplane[(int64_t)h_i*W+w_i] += add;
+            }
+            acc += g*pix;
+            iW += g*weight*sW*igW;
+            iH += g*weight*sH*igH;
+          }
+          gweights[fo] += acc;
+          ginds[fo*3+1] += iH*signH;
+          ginds[fo*3+2] += iW*signW;
+        }
+      }
+    }
+  }
+}

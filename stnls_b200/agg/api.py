@@ -1,9 +1,9 @@
 """Dict-config factory: agg = stnls_b200.agg.init(cfg)   (lib/stnls/agg/api.py:20-48).
 "wpsum" (the README name) resolves to gather_add, its successor in the reference."""
 from ..utils import extract_pairs
-from . import gather_add
+from . import gather, gather_add
 
-MENU = {"wpsum": gather_add, "gather_add": gather_add}
+MENU = {"wpsum": gather_add, "gather_add": gather_add, "gather": gather, "nlstack": gather}
 
 
 def _module(name):

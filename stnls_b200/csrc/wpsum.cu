@@ -25,6 +25,7 @@ struct AggParams {
   stnls_geom g;
   stnls_agg_opts o;
   int nquad;
+  int stack;         // 1: NonLocalGather -- no sum over K, slab (n*K + k) of out / gout belongs to neighbour k
   int64_t nthreads;
 };
 
@@ -40,6 +41,8 @@ __global__ void __launch_bounds__(128) wpsum_fwd_kernel(const __grid_constant__ 
   const int w = (int)(r % W); r /= W;
   const int h = (int)(r % H); r /= H;
   const int tl = (int)(r % g.Tq); r /= g.Tq;
+  int k_lo = 0, k_hi = o.K;
+  if (P.stack) { k_lo = (int)(r % o.K); k_hi = k_lo + 1; r /= o.K; }   // thread order [n][k][t][h][w][quad]
   const int n = (int)r;
   const int t = tl + g.tq0;
   const int64_t vfs = (int64_t)H * W * g.Fp;
@@ -58,7 +61,7 @@ __global__ void __launch_bounds__(128) wpsum_fwd_kernel(const __grid_constant__ 
       const int nw = wq / o.stride0;
       if (nw >= g.nW) continue;
       const int64_t qb = ((((int64_t)n * g.Tq + tl) * g.nH + nh) * g.nW + nw) * o.K;
-      for (int ki = 0; ki < o.K; ki++) {
+      for (int ki = k_lo; ki < k_hi; ki++) {
         const float weight = P.weights[qb + ki];
         if (INT) {
           const int* f = reinterpret_cast<const int*>(P.flows) + (qb + ki) * 3;
@@ -87,7 +90,8 @@ __global__ void __launch_bounds__(128) wpsum_fwd_kernel(const __grid_constant__ 
   }
   const float cnt = (float)(P.counts_h[h] * P.counts_w[w]);
   float4 o4 = make_float4(acc.x / cnt, acc.y / cnt, acc.z / cnt, acc.w / cnt);
-  *reinterpret_cast<float4*>(P.out + (((int64_t)n * g.Tq + tl) * H + h) * W * g.Fp + (int64_t)w * g.Fp + c4) = o4;
+  const int64_t slab = P.stack ? (int64_t)n * o.K + k_lo : n;
+  *reinterpret_cast<float4*>(P.out + ((slab * g.Tq + tl) * H + h) * W * g.Fp + (int64_t)w * g.Fp + c4) = o4;
 }
 
 __device__ __forceinline__ float dot4(const float4 a, const float4 b) {
@@ -123,7 +127,7 @@ __global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant
   const int64_t vfs = (int64_t)H * W * g.Fp;
   const float* vb = P.v + (int64_t)n * g.Tk * vfs + c4;
   float* gvb = P.out + (int64_t)n * g.Tk * vfs + c4;
-  const float* gof = P.gout + ((int64_t)n * g.Tq + tl) * vfs + c4;
+  const float* gof = P.gout + ((P.stack ? (int64_t)n * o.K + k_lo : (int64_t)n) * g.Tq + tl) * vfs + c4;  // stack => KSPLIT
 
   // generic path for one neighbour: every patch pixel validated / reflected on its own
   // (gather_add_kernel.cu:201-319 int, :369-514 + shared_kernel.cu:773-827 float)
@@ -187,7 +191,14 @@ __global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant
           if (!(inb(r2, W) && inb(n2, W))) continue;
           const float4 gr = ldg4(gof + ((int64_t)r1 * W + r2) * g.Fp);
           const float4 wg = f4scale(gr, weight);
-          const Taps tp = make_taps(n1, n2, H, W);
+          Taps tp = make_taps(n1, n2, H, W);
+          if (P.stack) {  // NonLocalGather's backward reflects a tap outside the frame (gather_bilin2d.cu:188-189)
+#pragma unroll
+            for (int x = 0; x < 2; x++) {
+              tp.h[x] = bnd(tp.h[x], H); tp.vh[x] = inb(tp.h[x], H);
+              tp.w[x] = bnd(tp.w[x], W); tp.vw[x] = inb(tp.w[x], W);
+            }
+          }
           float aH = 0.f, aW = 0.f;
 #pragma unroll
           for (int ix = 0; ix < 2; ix++) {
@@ -309,15 +320,16 @@ int agg_check(const stnls_geom* g, const stnls_agg_opts* o, const char* who) {
 
 }  // namespace
 
-extern "C" int stnls_wpsum_forward(float* out_cl, const float* v_cl, const float* weights, const void* flows,
-                                   const int* counts_h, const int* counts_w, const stnls_geom* g,
-                                   const stnls_agg_opts* o, stnls_stream_t stream) {
+static int agg_forward(float* out_cl, const float* v_cl, const float* weights, const void* flows,
+                       const int* counts_h, const int* counts_w, const stnls_geom* g,
+                       const stnls_agg_opts* o, stnls_stream_t stream, int stack) {
   if (int rc = agg_check(g, o, "wpsum_forward")) return rc;
   STNLS_REQUIRE(out_cl && v_cl && weights && flows && counts_h && counts_w, "wpsum_forward: null argument");
   AggParams P = {};
   P.out = out_cl; P.v = v_cl; P.weights = weights; P.flows = flows; P.counts_h = counts_h; P.counts_w = counts_w;
   P.g = *g; P.o = *o; P.nquad = g->Fp / 4;
-  P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->kH * g->kW * P.nquad;
+  P.stack = stack;
+  P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->kH * g->kW * P.nquad * (stack ? o->K : 1);
   if (P.nthreads == 0) return STNLS_OK;
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_forward: too many threads for one launch");
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
@@ -328,9 +340,20 @@ extern "C" int stnls_wpsum_forward(float* out_cl, const float* v_cl, const float
   return STNLS_OK;
 }
 
-extern "C" int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* grad_flows, const float* gout_cl,
-                                    const float* v_cl, const float* weights, const void* flows,
-                                    const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream) {
+extern "C" int stnls_wpsum_forward(float* out_cl, const float* v_cl, const float* weights, const void* flows,
+                                   const int* counts_h, const int* counts_w, const stnls_geom* g,
+                                   const stnls_agg_opts* o, stnls_stream_t stream) {
+  return agg_forward(out_cl, v_cl, weights, flows, counts_h, counts_w, g, o, stream, 0);
+}
+extern "C" int stnls_gather_forward(float* stack_cl, const float* v_cl, const float* weights, const void* flows,
+                                    const int* counts_h, const int* counts_w, const stnls_geom* g,
+                                    const stnls_agg_opts* o, stnls_stream_t stream) {
+  return agg_forward(stack_cl, v_cl, weights, flows, counts_h, counts_w, g, o, stream, 1);
+}
+
+static int agg_backward(float* gv_cl, float* grad_weights, float* grad_flows, const float* gout_cl,
+                        const float* v_cl, const float* weights, const void* flows,
+                        const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream, int stack) {
   if (int rc = agg_check(g, o, "wpsum_backward")) return rc;
   STNLS_REQUIRE(gv_cl && grad_weights && gout_cl && v_cl && weights && flows, "wpsum_backward: null argument");
   STNLS_REQUIRE(o->itype_int || grad_flows, "wpsum_backward: grad_flows required for itype float");
@@ -343,7 +366,8 @@ extern "C" int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* gr
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
   cudaStream_t st = (cudaStream_t)stream;
   const bool fast3 = (o->ps == 3 && o->dilation == 1 && !getenv("STNLS_NO_FAST3"));
-  const bool ksplit = o->ps >= 2 && getenv("STNLS_WPB_NO_KSPLIT") == nullptr;  // default on: 0.47 -> 0.29 ms on C2
+  P.stack = stack;
+  const bool ksplit = stack || (o->ps >= 2 && getenv("STNLS_WPB_NO_KSPLIT") == nullptr);  // default on: 0.47 -> 0.29 ms on C2
   if (ksplit) {
     P.nthreads *= o->K;
     STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_backward: too many threads for one launch");
@@ -361,4 +385,15 @@ extern "C" int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* gr
   }
   STNLS_CHECK_LAUNCH("wpsum_backward");
   return STNLS_OK;
+}
+
+extern "C" int stnls_wpsum_backward(float* gv_cl, float* grad_weights, float* grad_flows, const float* gout_cl,
+                                    const float* v_cl, const float* weights, const void* flows,
+                                    const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream) {
+  return agg_backward(gv_cl, grad_weights, grad_flows, gout_cl, v_cl, weights, flows, g, o, stream, 0);
+}
+extern "C" int stnls_gather_backward(float* gv_cl, float* grad_weights, float* grad_flows, const float* gstack_cl,
+                                     const float* v_cl, const float* weights, const void* flows,
+                                     const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream) {
+  return agg_backward(gv_cl, grad_weights, grad_flows, gstack_cl, v_cl, weights, flows, g, o, stream, 1);
 }

@@ -184,6 +184,26 @@ def wpsum_backward(gout_cl, v_cl, weights, flows, geom, opts):
     return gv, gw, gf
 
 
+def gather_forward(v_cl, weights, flows, counts, geom, opts):
+    """NonLocalGather forward: (N*K, Tq, H, W, Fp), slab n*K + k = neighbour k."""
+    _need_cuda(v_cl, weights, flows)
+    g = geom
+    out = th.empty((g.B * g.HD * opts.K, g.Tq, g.kH, g.kW, g.Fp), device=v_cl.device, dtype=th.float32)
+    _launch("gather_forward", _C.lib().stnls_gather_forward, _ptr(out), _ptr(v_cl), _ptr(weights), _ptr(flows),
+            _ptr(counts[0]), _ptr(counts[1]), ctypes.byref(g), ctypes.byref(opts), _stream())
+    return out
+
+
+def gather_backward(gstack_cl, v_cl, weights, flows, geom, opts):
+    _need_cuda(gstack_cl, v_cl, weights, flows)
+    gv = th.zeros_like(v_cl)
+    gw = th.zeros_like(weights)
+    gf = None if opts.itype_int else th.zeros(flows.shape, device=flows.device, dtype=th.float32)
+    _launch("gather_backward", _C.lib().stnls_gather_backward, _ptr(gv), _ptr(gw), _ptr(gf), _ptr(gstack_cl),
+            _ptr(v_cl), _ptr(weights), _ptr(flows), ctypes.byref(geom), ctypes.byref(opts), _stream())
+    return gv, gw, gf
+
+
 def add_inplace(dst, src):
     assert dst.is_contiguous() and src.is_contiguous() and dst.numel() == src.numel()
     _launch("add_inplace", _C.lib().stnls_add_inplace, _ptr(dst), _ptr(src), dst.numel(), _stream())
