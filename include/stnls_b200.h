@@ -147,6 +147,18 @@ int stnls_gather_backward(float* gv_cl, float* grad_weights, float* grad_flows,
                           const void* flows, const stnls_geom* g, const stnls_agg_opts* o,
                           stnls_stream_t stream);
 
+/* ---- search_flow (accumulated per-query flows) ---------------------------------------
+ * replaces  search_flow_forward / search_flow_backward (lib/csrc/nn/search_flow.cpp:29-58, kernels
+ *           lib/csrc/nn/search_flow_kernel.cu), driven by lib/stnls/nn/search_flow.py:24-96.
+ *  fflow, bflow (B,T,2,H,W): optical flow t->t+1 / t->t-1, channel 0 = dw, 1 = dh
+ *  flows (B,T,W_t-1,2,nH,nW), W_t = min(2*wt+1,T): written (forward) / read (backward)
+ *  grad_fflow, grad_bflow (B,T,2,H,W): pre-zeroed accumulators                                       */
+int stnls_search_flow_forward(float* flows, const float* fflow, const float* bflow, int B, int T,
+                              int H, int W, int wt, int stride0, stnls_stream_t stream);
+int stnls_search_flow_backward(float* grad_fflow, float* grad_bflow, const float* grad_flows,
+                               const float* fflow, const float* bflow, const float* flows, int B,
+                               int T, int H, int W, int wt, int stride0, stnls_stream_t stream);
+
 /* separable patch-overlap counts (host helper, no GPU): counts_h[h] = #{(nh,pi): nh*stride0 +
  * dilation*(pi+patch_offset) == h}; equals what gather_add_forward_kernel counts atomically
  * (lib/csrc/agg/gather_add_kernel.cu:94-97).  Returns the minimum count (0 => reference asserts). */

@@ -366,3 +366,27 @@ def gather_backward(grad_stack, vid, weights, inds, counts, ps, stride0, dilatio
     if gi is not None:
         gi = gi.reshape(weights.shape + (3,))
     return gvid, gw, gi
+
+
+# ---------------------------------------------------------------------------------------------
+#   search_flow: lib/stnls/nn/search_flow.py:24-96
+# ---------------------------------------------------------------------------------------------
+
+def search_flow_forward(fflow, bflow, wt, stride0=1):
+    fflow, bflow = fflow.contiguous().float(), bflow.contiguous().float()
+    B, T, _, H, W = fflow.shape
+    nH, nW = (H - 1) // stride0 + 1, (W - 1) // stride0 + 1
+    W_t = min(2 * wt + 1, T)
+    flows = th.zeros((B, T, W_t - 1, 2, nH, nW), dtype=th.float32)
+    if wt > 0:
+        lib().oracle_search_flow_forward(_p(flows), _p(fflow), _p(bflow), B, T, H, W, wt, stride0)
+    return flows
+
+
+def search_flow_backward(grad_flows, fflow, bflow, flows, wt, stride0=1):
+    fflow, bflow = fflow.contiguous().float(), bflow.contiguous().float()
+    B, T, _, H, W = fflow.shape
+    gf, gb = th.zeros_like(fflow), th.zeros_like(bflow)
+    lib().oracle_search_flow_backward(_p(gf), _p(gb), _p(grad_flows.contiguous().float()), _p(fflow), _p(bflow),
+                                      _p(flows.contiguous().float()), B, T, H, W, wt, stride0)
+    return gf, gb

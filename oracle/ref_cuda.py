@@ -238,3 +238,22 @@ def gather_backward(grad_stack, vid, weights, inds, counts, ps, stride0, dilatio
                                       reflect_bounds, patch_offset)
         gi = gi.reshape(weights.shape + (3,))
     return gvid, gw.reshape(weights.shape), gi
+
+
+def search_flow_forward(fflow, bflow, wt, stride0=1):
+    """Drives search_flow_forward as lib/stnls/nn/search_flow.py:47-67 does."""
+    fflow, bflow = fflow.contiguous(), bflow.contiguous()
+    B, T, _, H, W = fflow.shape
+    nH, nW = (H - 1) // stride0 + 1, (W - 1) // stride0 + 1
+    W_t = min(2 * wt + 1, T)
+    flows = th.zeros((B, T, W_t - 1, 2, nH, nW), device=fflow.device, dtype=fflow.dtype)
+    mod().search_flow_forward(fflow, bflow, flows, wt, stride0)
+    return flows
+
+
+def search_flow_backward(grad_flows, fflow, bflow, flows, wt, stride0=1):
+    """lib/stnls/nn/search_flow.py:69-96"""
+    gf, gb = th.zeros_like(fflow), th.zeros_like(bflow)
+    mod().search_flow_backward(gf, gb, grad_flows.contiguous(), fflow.contiguous(), bflow.contiguous(),
+                               flows.contiguous(), wt, stride0)
+    return gf, gb

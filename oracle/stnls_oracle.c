@@ -965,3 +965,119 @@ void oracle_gather_backward(float* gvid, float* gweights, float* ginds,
     }
   }
 }
+
+/*
+ * search_flow: chain frame-to-frame optical flows through the temporal window.
+ *   forward : lib/csrc/nn/search_flow_kernel.cu:17-88 + lib/csrc/nn/shared_flows.cu:39-72
+ *   backward: lib/csrc/nn/search_flow_kernel.cu:131-250 + lib/csrc/nn/shared_flows.cu:108-290
+ * fflow,bflow (B,T,2,H,W); flows (B,T,W_t-1,2,nH,nW), W_t = min(2wt+1,T).
+ * A tap still outside the frame after one reflection (an out-of-bounds read in the reference) is clamped.
+ */
+static inline int clamp_i(int v, int lim){ return v < 0 ? 0 : (v > lim-1 ? lim-1 : v); }
+
+static void flow_hop(float* hc, float* wc, const float* flow, int H, int W){
+  float h0 = *hc, w0 = *wc;
+  for (int i=0;i<2;i++) for (int j=0;j<2;j++){
+    int hj = (int)floorf(h0+i), wj = (int)floorf(w0+j);
+    float weight = fmaxf(0.f,1-fabsf(hj-h0)) * fmaxf(0.f,1-fabsf(wj-w0));
+    hj = clamp_i(bounds_i(hj,H),H); wj = clamp_i(bounds_i(wj,W),W);
+    *wc = fmaf(weight, flow[(int64_t)hj*W+wj], *wc);
+    *hc = fmaf(weight, flow[(int64_t)H*W+(int64_t)hj*W+wj], *hc);
+  }
+}
+
+void oracle_search_flow_forward(float* flows, const float* fflow, const float* bflow,
+                                int B, int T, int H, int W, int wt, int stride0){
+  int nH=(H-1)/stride0+1, nW=(W-1)/stride0+1, nHW=nH*nW;
+  int W_t = (2*wt+1 < T) ? 2*wt+1 : T;
+  int64_t fs = 2LL*H*W;
+  #pragma omp parallel for collapse(2) schedule(static)
+  for (int b=0;b<B;b++) for (int qi=0; qi<T*nHW; qi++){
+    int ref[3]; pixel_loc(ref,qi,stride0,nW,nHW,H,W);
+    int ti=ref[0], hn=ref[1]/stride0, wn=ref[2]/stride0;
+    float h_ref=(float)ref[1], w_ref=(float)ref[2], hc=h_ref, wc=w_ref;
+    int t_max = time_tmax(ti,T,wt);
+    for (int si=1; si<W_t; si++){
+      int tj = ti+si;
+      int swap = (ti+si-1)==t_max;
+      tj = (tj>t_max) ? t_max-si : tj;
+      if (swap){ hc=h_ref; wc=w_ref; }
+      const float* flow = (tj>ti) ? fflow+((int64_t)b*T+(tj-1))*fs : bflow+((int64_t)b*T+(tj+1))*fs;
+      flow_hop(&hc,&wc,flow,H,W);
+      int64_t o = ((((int64_t)b*T+ti)*(W_t-1)+(si-1))*2)*nHW + (int64_t)hn*nW+wn;
+      flows[o+nHW] = hc-h_ref;
+      flows[o] = wc-w_ref;
+    }
+  }
+}
+
+static void flow_update_weights(float* dAdF0, float* dAdF1, float p1, float p2, int H, int W, const float* flow){
+  float dF[2][2] = {{0,0},{0,0}};
+  int sH = inb_f(p1,H)?1:-1, sW = inb_f(p2,W)?1:-1;
+  p1 = bounds_f(p1,H); p2 = bounds_f(p2,W);
+  for (int ix=0;ix<2;ix++) for (int jx=0;jx<2;jx++){
+    int i0 = (int)(ix==0 ? floorf(p1) : floorf(p1)+1);
+    float gH = fmaxf(0.f,1-fabsf(i0-p1));
+    int i1 = (int)(jx==0 ? floorf(p2) : floorf(p2)+1);
+    float gW = fmaxf(0.f,1-fabsf(i1-p2));
+    if (!inb_i(i0,H) || !inb_i(i1,W)) continue;
+    float vW = flow[(int64_t)i0*W+i1], vH = flow[(int64_t)H*W+(int64_t)i0*W+i1];
+    dF[0][0] += (jx==0) ? -gH*vW : gH*vW;
+    dF[0][1] += (ix==0) ? -gW*vW : gW*vW;
+    dF[1][0] += (jx==0) ? -gH*vH : gH*vH;
+    dF[1][1] += (ix==0) ? -gW*vH : gW*vH;
+  }
+  float a0=dAdF0[0], a1=dAdF0[1], b0=dAdF1[0], b1=dAdF1[1];
+  dAdF0[0] += dF[0][0]*sW*a0 + dF[0][1]*sH*a1;
+  dAdF0[1] += dF[1][0]*sW*a0 + dF[1][1]*sH*a1;
+  dAdF1[0] += dF[0][0]*sW*b0 + dF[0][1]*sH*b1;
+  dAdF1[1] += dF[1][0]*sW*b0 + dF[1][1]*sH*b1;
+}
+
+void oracle_search_flow_backward(float* gfflow, float* gbflow, const float* gflows,
+                                 const float* fflow, const float* bflow, const float* flows,
+                                 int B, int T, int H, int W, int wt, int stride0){
+  int nH=(H-1)/stride0+1, nW=(W-1)/stride0+1, nHW=nH*nW;
+  int W_t = (2*wt+1 < T) ? 2*wt+1 : T;
+  int64_t fs = 2LL*H*W;
+  /* serial over queries: the scatter targets overlap (the reference uses atomics) */
+  for (int b=0;b<B;b++) for (int qi=0; qi<T*nHW; qi++) for (int si=1; si<=W_t; si++){
+    int ref[3]; pixel_loc(ref,qi,stride0,nW,nHW,H,W);
+    int ti=ref[0], nh=ref[1]/stride0, nw=ref[2]/stride0;
+    int t_shift = (ti-wt<0 ? ti-wt : 0) + (ti+wt-(T-1)>0 ? ti+wt-(T-1) : 0);
+    int t_min = ti-wt-t_shift; if (t_min<0) t_min=0;
+    int t_max = ti+wt-t_shift; if (t_max>T-1) t_max=T-1;
+    int tj = ti+si; tj = (tj>t_max) ? t_max-si : tj;
+    int isFwd = tj>ti;
+    int t_flow = isFwd ? tj-1 : tj+1;
+    const float* flow = (isFwd?fflow:bflow)+(int64_t)b*T*fs;
+    float* g_flow = (isFwd?gfflow:gbflow)+(int64_t)b*T*fs;
+    int t_inc = isFwd?1:-1;
+    int t_end = isFwd ? (t_max-tj+1) : (tj-t_min+1);
+    if (t_end <= 0) continue;                    /* si == W_t: the reference thread does nothing */
+    int adjacent = abs(ti-tj)==1;
+    const float* fl = flows + (((int64_t)b*T+ti)*(W_t-1))*2*nHW + (int64_t)nh*nW+nw;
+    const float* gf = gflows + (((int64_t)b*T+ti)*(W_t-1))*2*nHW + (int64_t)nh*nW+nw;
+    float r1=(float)ref[1], r2=(float)ref[2];
+    if (!adjacent){ r1 = ref[1]+fl[((int64_t)(si-2)*2+1)*nHW]; r2 = ref[2]+fl[((int64_t)(si-2)*2)*nHW]; }
+    float dAdF0[2], dAdF1[2];
+    for (int tx=0; tx<t_end; tx++){
+      float gvW = gf[((int64_t)(si-1+tx)*2)*nHW], gvH = gf[((int64_t)(si-1+tx)*2+1)*nHW];
+      if (tx==0){ dAdF0[0]=1; dAdF0[1]=0; dAdF1[0]=0; dAdF1[1]=1; }
+      else{
+        float p1 = (float)ref[1]+fl[((int64_t)(si+tx-2)*2+1)*nHW], p2 = (float)ref[2]+fl[((int64_t)(si+tx-2)*2)*nHW];
+        flow_update_weights(dAdF0,dAdF1,p1,p2,H,W,flow+(int64_t)(t_flow+t_inc*tx)*fs);
+      }
+      float* g = g_flow+(int64_t)t_flow*fs;
+      float v0 = dAdF0[0]*gvW+dAdF0[1]*gvH, v1 = dAdF1[0]*gvW+dAdF1[1]*gvH;
+      for (int ix=0;ix<2;ix++) for (int jx=0;jx<2;jx++){     /* assign_bilin2d, shared_flows.cu:108-141 */
+        int i0 = (int)floorf(r1+ix); float gH = fmaxf(0.f,1-fabsf(i0-r1));
+        int i1 = (int)floorf(r2+jx); float gW = fmaxf(0.f,1-fabsf(i1-r2));
+        float w = gH*gW;
+        i0 = clamp_i(bounds_i(i0,H),H); i1 = clamp_i(bounds_i(i1,W),W);
+        g[(int64_t)i0*W+i1] += w*v0;
+        g[(int64_t)H*W+(int64_t)i0*W+i1] += w*v1;
+      }
+    }
+  }
+}

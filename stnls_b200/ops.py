@@ -204,6 +204,40 @@ def gather_backward(gstack_cl, v_cl, weights, flows, geom, opts):
     return gv, gw, gf
 
 
+def _flow_check(fflow, bflow):
+    _need_cuda(fflow, bflow)
+    if fflow.dim() != 5 or fflow.shape[2] != 2 or fflow.shape != bflow.shape:
+        raise ValueError("search_flow: fflow and bflow must both be (B,T,2,H,W)")
+    if fflow.dtype != th.float32 or bflow.dtype != th.float32:
+        raise TypeError("stnls_b200 supports float32 flows only")
+
+
+def search_flow_forward(fflow, bflow, wt, stride0):
+    """(B,T,2,H,W) x2 -> accumulated flows (B,T,W_t-1,2,nH,nW), W_t = min(2wt+1,T)."""
+    _flow_check(fflow, bflow)
+    fflow, bflow = fflow.contiguous(), bflow.contiguous()
+    B, T, _, H, W = fflow.shape
+    nH, nW = (H - 1) // stride0 + 1, (W - 1) // stride0 + 1
+    W_t = min(2 * wt + 1, T)
+    flows = th.empty((B, T, W_t - 1, 2, nH, nW), device=fflow.device, dtype=th.float32)
+    if flows.numel():
+        _launch("search_flow_forward", _C.lib().stnls_search_flow_forward, _ptr(flows), _ptr(fflow), _ptr(bflow),
+                B, T, H, W, wt, stride0, _stream())
+    return flows
+
+
+def search_flow_backward(grad_flows, fflow, bflow, flows, wt, stride0):
+    _flow_check(fflow, bflow)
+    B, T, _, H, W = fflow.shape
+    gf, gb = th.zeros_like(fflow), th.zeros_like(bflow)
+    grad_flows = grad_flows.contiguous().float()
+    if flows.numel():
+        _launch("search_flow_backward", _C.lib().stnls_search_flow_backward, _ptr(gf), _ptr(gb), _ptr(grad_flows),
+                _ptr(fflow.contiguous()), _ptr(bflow.contiguous()), _ptr(flows.contiguous()),
+                B, T, H, W, wt, stride0, _stream())
+    return gf, gb
+
+
 def add_inplace(dst, src):
     assert dst.is_contiguous() and src.is_contiguous() and dst.numel() == src.numel()
     _launch("add_inplace", _C.lib().stnls_add_inplace, _ptr(dst), _ptr(src), dst.numel(), _stream())

@@ -164,8 +164,8 @@ class NonLocalSearch(th.nn.Module):
         assert self.wt >= 0, "Must have nonnegative time search window"
         vid0, vid1 = args[:2]
         if len(args) == 4:
-            raise NotImplementedError("stnls_b200: pass accumulated flows; search_flow(fflow,bflow) is a "
-                                      "next-row component (SURVEY.md 8f N1)")
+            from ..nn import search_flow  # lib/stnls/search/non_local_search.py:173-175
+            flows = search_flow(args[2], args[3], self.wt, self.stride0)
         elif len(args) == 3:
             flows = args[2]
         else:

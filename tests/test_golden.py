@@ -12,7 +12,7 @@ import torch as th
 from util import assert_close, assert_topk_equal
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-FILES = sorted(glob.glob(os.path.join(HERE, "golden", "*.npz")))
+FILES = sorted(glob.glob(os.path.join(HERE, "golden", "nls_*.npz")))
 CFG = {
     "nls_int_prod": dict(itype="int", dist_type="prod", stride1=1, self_action="anchor", k=6),
     "nls_int_l2": dict(itype="int", dist_type="l2", stride1=1, self_action=None, k=6),
