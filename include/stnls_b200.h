@@ -159,6 +159,16 @@ int stnls_search_flow_backward(float* grad_fflow, float* grad_bflow, const float
                                const float* fflow, const float* bflow, const float* flows, int B,
                                int T, int H, int W, int wt, int stride0, stnls_stream_t stream);
 
+/* ---- fused normalise step --------------------------------------------------------
+ * replaces  SoftmaxNormalize (lib/stnls/normz/softmax.py:21-42) / `softmax(10*dists,-1)` (README.md:51):
+ *   weights[r, k] = softmax_k(scale * dists[r, k]),  k < K;  dists rows have Kin >= K entries (k_agg slice),
+ *   `scale` carries the sign (negative for l2 distances).  K <= 64.
+ *  backward: grad_dists (rows, Kin) fully written (zeros for k >= K).                                    */
+int stnls_softmax_forward(float* weights, const float* dists, int64_t rows, int K, int Kin,
+                          float scale, stnls_stream_t stream);
+int stnls_softmax_backward(float* grad_dists, const float* grad_weights, const float* weights,
+                           int64_t rows, int K, int Kin, float scale, stnls_stream_t stream);
+
 /* separable patch-overlap counts (host helper, no GPU): counts_h[h] = #{(nh,pi): nh*stride0 +
  * dilation*(pi+patch_offset) == h}; equals what gather_add_forward_kernel counts atomically
  * (lib/csrc/agg/gather_add_kernel.cu:94-97).  Returns the minimum count (0 => reference asserts). */

@@ -36,6 +36,7 @@ EXPORTS = ["stnls_last_error", "stnls_version", "stnls_pack_cl", "stnls_unpack_c
            "stnls_search_forward", "stnls_search_backward", "stnls_wpsum_forward",
            "stnls_wpsum_backward", "stnls_gather_forward", "stnls_gather_backward",
            "stnls_search_flow_forward", "stnls_search_flow_backward",
+           "stnls_softmax_forward", "stnls_softmax_backward",
            "stnls_overlap_counts", "stnls_add_inplace"]
 
 _lib = None
@@ -67,6 +68,8 @@ def lib():
     L.stnls_gather_backward.argtypes = [c_vp] * 7 + [P(Geom), P(AggOpts), c_vp]
     L.stnls_search_flow_forward.argtypes = [c_vp] * 3 + [c_int] * 6 + [c_vp]
     L.stnls_search_flow_backward.argtypes = [c_vp] * 6 + [c_int] * 6 + [c_vp]
+    L.stnls_softmax_forward.argtypes = [c_vp, c_vp, c_i64, c_int, c_int, c_f32, c_vp]
+    L.stnls_softmax_backward.argtypes = [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_f32, c_vp]
     L.stnls_overlap_counts.argtypes = [c_vp] + [c_int] * 6
     L.stnls_add_inplace.argtypes = [c_vp, c_vp, c_i64, c_vp]
     for name in EXPORTS:

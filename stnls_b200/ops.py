@@ -10,6 +10,7 @@ from . import _C
 from ._C import AggOpts, Geom, SearchOpts
 
 MAX_FUSED_K = 32
+MAX_SOFTMAX_K = 64
 
 # launch accounting: every C-ABI call below launches exactly one of our kernels.  `LAUNCHES` counts
 # them; when `TIMELINE` is a list, each launch is bracketed by CUDA events on the launching stream
@@ -236,6 +237,29 @@ def search_flow_backward(grad_flows, fflow, bflow, flows, wt, stride0):
                 _ptr(fflow.contiguous()), _ptr(bflow.contiguous()), _ptr(flows.contiguous()),
                 B, T, H, W, wt, stride0, _stream())
     return gf, gb
+
+
+def softmax_forward(dists, K, scale):
+    """weights = softmax(scale * dists[..., :K], -1) in one kernel (dists contiguous, last dim Kin >= K)."""
+    _need_cuda(dists)
+    assert dists.is_contiguous() and dists.dtype == th.float32
+    Kin = dists.shape[-1]
+    rows = dists.numel() // Kin
+    out = th.empty(tuple(dists.shape[:-1]) + (K,), device=dists.device, dtype=th.float32)
+    _launch("softmax_forward", _C.lib().stnls_softmax_forward, _ptr(out), _ptr(dists), rows, K, Kin,
+            float(scale), _stream())
+    return out
+
+
+def softmax_backward(grad_weights, weights, Kin, scale):
+    _need_cuda(grad_weights, weights)
+    K = weights.shape[-1]
+    rows = weights.numel() // K
+    grad_weights = grad_weights.contiguous().float()
+    gd = th.empty(tuple(weights.shape[:-1]) + (Kin,), device=weights.device, dtype=th.float32)
+    _launch("softmax_backward", _C.lib().stnls_softmax_backward, _ptr(gd), _ptr(grad_weights), _ptr(weights),
+            rows, K, Kin, float(scale), _stream())
+    return gd
 
 
 def add_inplace(dst, src):

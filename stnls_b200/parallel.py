@@ -13,6 +13,8 @@ all-gather of full tensors.
 import torch as th
 import torch.distributed as dist
 
+from .normz.softmax import softmax_scaled
+
 
 def shard_frames(T, world, rank):
     """Contiguous, balanced partition of T frames: returns [a, b)."""
@@ -265,6 +267,6 @@ class ShardedSearchAgg(th.nn.Module):
         v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
         dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
         sign = -1.0 if self.search.dist_type == "l2" else 1.0
-        weights = th.softmax(sign * self.scale * dists, -1)
+        weights = softmax_scaled(dists, sign * self.scale)   # fused sign/scale/softmax (normz)
         out = self.agg(v_ext, weights, inds, shard=self.plan.shard)
         return out, dists, inds
