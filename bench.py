@@ -240,10 +240,12 @@ def run_product(args):
 
     # ---- value: inputs resident in HBM -------------------------------------------------------
     resident = [t.to(dev) for t in host]
+    # the timed steps' inputs are cloned BEFORE the warm-up so that the warm-up steps grow the caching
+    # allocator to its steady-state size (otherwise the first timed step pays for cudaMalloc)
+    fresh = [[t.detach().clone() for t in resident] for _ in range(args.steps)]
     for _ in range(args.warmup):
         step(*[t.detach().clone() for t in resident])
     barrier()
-    fresh = [[t.detach().clone() for t in resident] for _ in range(args.steps)]
     evs = []
     ops.TIMELINE = []
     launches0 = ops.LAUNCHES
@@ -260,6 +262,8 @@ def run_product(args):
     launches = ops.LAUNCHES - launches0
     timeline, ops.TIMELINE = ops.TIMELINE, None
     t_ms = sum(a.elapsed_time(b) for a, b in evs)
+    if os.environ.get("BENCH_DEBUG"):
+        print(f"[rank {rank}] per-step ms:", [round(a.elapsed_time(b), 3) for a, b in evs], file=sys.stderr, flush=True)
     del fresh
 
     # ---- e2e: pinned host buffers in, results back to pinned host buffers ----------------------
