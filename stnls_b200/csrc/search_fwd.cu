@@ -239,6 +239,11 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
   const char* env_w = getenv("STNLS_FWD_WARPS");
   C.wpb = env_w ? atoi(env_w) : 8;
   if (C.wpb < 1 || C.wpb > 8) C.wpb = 8;
+  // bank-conflict-free candidate order needs an odd lattice step per candidate (and the odd row pitch Mp)
+  C.W8 = ((C.n1 & 1) && !getenv("STNLS_FWD_ROWMAJOR")) ? (wsz & ~7) : 0;
+  if (wsz < 8) C.W8 = 0;
+  C.nA = wsz * C.W8;
+  C.inv_W8 = C.W8 ? 1.f / C.W8 : 0.f;
   C.inv_G = 1.f / P.G; C.inv_wsz = 1.f / wsz; C.inv_Q4 = 1.f / C.Q4; C.inv_M = 1.f / C.M;
   return (size_t)C.warp_f4 * 16 <= 24 * 1024;
 }

@@ -20,6 +20,8 @@ struct TabCfg {
   int wpb;        // warps per block
   float inv_G, inv_wsz, inv_Q4, inv_M;
   int D;          // lattice denominator (u = 1/D)
+  int W8, nA;     // candidate enumeration: columns [0,W8) row-wise in chunks of 8 (nA = wsz*W8 lanes), rest column-wise
+  float inv_W8;
 };
 
 // one per translation unit; each picks dist_type / ps / channel-quad template variants at run time

@@ -296,10 +296,17 @@ __global__ void __launch_bounds__(256, (PS * PS * Q4T >= 36 || Q4T == 0) ? 3 : 4
       const bool active = base + lane < nC;
       const int posb = min(base + lane, nC - 1);
       const int gl = (C.nb == 1) ? 0 : fdiv(posb, C.inv_G);
-      const int s = posb - gl * P.G;
+      // lane -> candidate inside the group.  With W8 > 0 the first wsz*W8 lanes walk rows in chunks of W8
+      // (a multiple of 8) columns and the rest walks the leftover columns top to bottom, so the eight lanes
+      // of one LDS.128 wavefront read eight different 16-byte bank groups of T (row pitch Mp is odd)
+      const int e = posb - gl * P.G;
+      int wi, wj;
+      if (C.W8 == 0) { wi = fdiv(e, C.inv_wsz); wj = e - wi * P.wsz; }
+      else if (e < C.nA) { wi = fdiv(e, C.inv_W8); wj = e - wi * C.W8; }
+      else { const int e2 = e - C.nA; const int cc = fdiv(e2, C.inv_wsz); wi = e2 - cc * P.wsz; wj = C.W8 + cc; }
+      const int s = wi * P.wsz + wj;
       const int gq = g0 + gl;
       const int pos = gq * P.G + s;
-      const int wi = fdiv(s, C.inv_wsz), wj = s - wi * P.wsz;
       Group<CC> gp = shfl_group(mine, gl);
       const int ag = (REFINE && anchored) ? __shfl_sync(FULL_MASK, my_ag, gl) : 0;
       CC chh, cww;
