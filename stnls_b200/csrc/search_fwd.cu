@@ -207,6 +207,13 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
   for (int sft = 0; sft < 8; sft++) if ((1 << sft) == C.Q4) C.q4sh = sft;
   C.ax_rounds = (C.M <= 16) ? 1 : 2;
   C.Mp = C.M | 1;
+  // small windows (ws < 8) keep the row-major candidate order; a row pitch == ws (mod 8) then puts eight
+  // consecutive candidates on eight different 16-byte bank groups.  Only when the padding is modest.
+  if (wsz < 8 && (C.n1 & 1) && !getenv("STNLS_FWD_NOPAD")) {
+    int mp = C.M;
+    while ((mp & 7) != (wsz & 7)) mp++;
+    if (mp <= C.M + 4) C.Mp = mp;
+  }
   int want = (C.Q4 == 2) ? 4 : (C.Q4 == 4) ? 2 : (C.Q4 >= 8 ? 1 : 0);
   C.PS4 = C.M * C.Mp;
   if (C.Q4 > 1) while ((C.PS4 & 7) != want) C.PS4++;
