@@ -101,6 +101,173 @@ __device__ __forceinline__ void axpy4(float4& y, float a, const float4 x) {
   y.x = fmaf(a, x.x, y.x); y.y = fmaf(a, x.y, y.y); y.z = fmaf(a, x.z, y.z); y.w = fmaf(a, x.w, y.w);
 }
 
+// ---- tiled forward for ps == 3, dilation == 1 (the README / 1080p shapes) ------------------------------
+// The gather kernel above redoes the whole (query, neighbour) setup -- flow read, reflection, bilinear taps --
+// for each of the 9 output pixels a patch covers.  Here a CTA owns a TH x TW tile of output pixels of one
+// frame: thread = (query whose patch touches the tile, channel quad) loops over the K neighbours ONCE,
+// keeps its 3x3 weighted patch in registers (interior neighbours: one shared 4x4 footprint, 16 loads), and
+// the patches are then summed into a shared-memory tile in 9 conflict-free phases (for a fixed patch pixel
+// the map query -> output pixel is injective), divided by the overlap counts and stored once.  Queries on
+// the tile rim are recomputed by the neighbouring CTA instead of exchanged -- still no atomics.
+struct TileCfg {
+  int TH, TW, nQh, nQw, tiles_w;
+};
+
+template <bool INT>
+__global__ void __launch_bounds__(512) wpsum_fwd_tile_kernel(const __grid_constant__ AggParams P,
+                                                             const __grid_constant__ TileCfg C) {
+  extern __shared__ float4 tile[];   // [TH][TW][nquad]
+  const stnls_geom& g = P.g;
+  const stnls_agg_opts& o = P.o;
+  const int H = g.kH, W = g.kW, Q4 = P.nquad, po = o.patch_offset, s0 = o.stride0;
+  const int tile_w = blockIdx.x % C.tiles_w, tile_h = blockIdx.x / C.tiles_w;
+  const int tl = blockIdx.y % g.Tq, n = blockIdx.y / g.Tq;
+  const int t = tl + g.tq0;
+  const int h0 = tile_h * C.TH, w0 = tile_w * C.TW;
+  for (int i = threadIdx.x; i < C.TH * C.TW * Q4; i += blockDim.x) tile[i] = f4zero();
+  __syncthreads();
+
+  const int c4 = threadIdx.x % Q4;
+  const int ql = threadIdx.x / Q4;
+  const int qlh = ql / C.nQw, qlw = ql - qlh * C.nQw;
+  const int xh = h0 - (2 + po), xw = w0 - (2 + po);            // first reference pixel whose patch reaches the tile
+  const int nh = (xh <= 0 ? 0 : (xh + s0 - 1) / s0) + qlh, nw = (xw <= 0 ? 0 : (xw + s0 - 1) / s0) + qlw;
+  const int rh = nh * s0, rw = nw * s0;                         // stride0 grids never wrap: nh*s0 <= H-1
+  const bool active = qlh < C.nQh && nh < g.nH && nw < g.nW && rh + po <= h0 + C.TH - 1 && rw + po <= w0 + C.TW - 1;
+
+  float4 acc[9];
+#pragma unroll
+  for (int i = 0; i < 9; i++) acc[i] = f4zero();
+  if (active) {
+    const int64_t vfs = (int64_t)H * W * g.Fp;
+    const float* vb = P.v + (int64_t)n * g.Tk * vfs + c4 * 4;
+    const int64_t qb = ((((int64_t)n * g.Tq + tl) * g.nH + nh) * g.nW + nw) * o.K;
+    const int64_t rs = (int64_t)W * g.Fp;
+    unsigned slow = 0;
+    // per-pixel path of one neighbour (reflected / clipped patches): gather_add_kernel.cu:76-123
+    auto slow_path = [&](float weight, float n0, float c1, float c2) {
+      const float* vf = vb + (int64_t)((int)n0 - g.tk0) * vfs;
+#pragma unroll
+      for (int pi = 0; pi < 3; pi++) {
+        float n1 = c1 + (float)(pi + po);
+        if (o.reflect_bounds) n1 = bnd(n1, H);
+        if (!inb(n1, H)) continue;
+#pragma unroll
+        for (int pj = 0; pj < 3; pj++) {   // unrolled: acc[] keeps compile-time indices and stays in registers
+          float n2 = c2 + (float)(pj + po);
+          if (o.reflect_bounds) n2 = bnd(n2, W);
+          if (!inb(n2, W)) continue;
+          const Taps tp = make_taps(n1, n2, H, W);
+          axpy4(acc[pi * 3 + pj], weight, interp4(vf - c4 * 4, tp, W, g.Fp, c4 * 4));
+        }
+      }
+    };
+    // the (weight, offset) of neighbour k+1 is fetched while neighbour k is processed
+    const int* fi = reinterpret_cast<const int*>(P.flows) + qb * 3;
+    float wnext = __ldg(P.weights + qb);
+    int x0 = __ldg(fi), x1 = __ldg(fi + 1), x2 = __ldg(fi + 2);
+    for (int ki = 0; ki < o.K; ki++) {
+      const float weight = wnext;
+      const int y0 = x0, y1 = x1, y2 = x2;
+      if (ki + 1 < o.K) {
+        wnext = __ldg(P.weights + qb + ki + 1);
+        x0 = __ldg(fi + (ki + 1) * 3); x1 = __ldg(fi + (ki + 1) * 3 + 1); x2 = __ldg(fi + (ki + 1) * 3 + 2);
+      }
+      if (INT) {
+        int n0 = t + y0, c1 = rh + y1, c2 = rw + y2;
+        if (!((abs(c1) < 1e7) && (abs(c2) < 1e7))) continue;
+        n0 = bnd(n0, g.T); c1 = bnd(c1, H); c2 = bnd(c2, W);
+        if (!inb(n0, g.T)) continue;
+        const float* vf = vb + (int64_t)(n0 - g.tk0) * vfs;
+#pragma unroll
+        for (int pi = 0; pi < 3; pi++) {
+          int n1 = c1 + pi + po;
+          if (o.reflect_bounds) n1 = bnd(n1, H);
+          if (!inb(n1, H)) continue;
+#pragma unroll
+          for (int pj = 0; pj < 3; pj++) {
+            int n2 = c2 + pj + po;
+            if (o.reflect_bounds) n2 = bnd(n2, W);
+            if (!inb(n2, W)) continue;
+            axpy4(acc[pi * 3 + pj], weight, ldg4(vf + (int64_t)n1 * rs + (int64_t)n2 * g.Fp));
+          }
+        }
+      } else {
+        float n0 = (float)t + __int_as_float(y0), c1 = (float)rh + __int_as_float(y1), c2 = (float)rw + __int_as_float(y2);
+        if (!((fabsf(c1) < 1e7) && (fabsf(c2) < 1e7))) continue;
+        n0 = bnd(n0, g.T); c1 = bnd(c1, H); c2 = bnd(c2, W);
+        if (!inb(n0, g.T)) continue;
+        const float* vf = vb + (int64_t)((int)n0 - g.tk0) * vfs;
+        // interior neighbour: all 9 patch pixels unreflected, their taps inside one 4x4 footprint
+        const int hh = __float2int_rz(c1 + (float)po), ww = __float2int_rz(c2 + (float)po);
+        float gh[3][2], gw[3][2];
+        bool ok = true;
+#pragma unroll
+        for (int p = 0; p < 3; p++) {
+          const float n1 = c1 + (float)(p + po), n2 = c2 + (float)(p + po);
+          const int a0 = __float2int_rz(n1), a1 = __float2int_rz(n1 + 1);
+          const int b0 = __float2int_rz(n2), b1 = __float2int_rz(n2 + 1);
+          ok = ok && (n1 >= 0) && (a0 == hh + p) && (a1 == hh + p + 1) && (a1 <= H - 1) && (n1 <= (float)(H - 1));
+          ok = ok && (n2 >= 0) && (b0 == ww + p) && (b1 == ww + p + 1) && (b1 <= W - 1) && (n2 <= (float)(W - 1));
+          gh[p][0] = fmaxf(0.f, 1 - fabsf(a0 - n1)); gh[p][1] = fmaxf(0.f, 1 - fabsf(a1 - n1));
+          gw[p][0] = fmaxf(0.f, 1 - fabsf(b0 - n2)); gw[p][1] = fmaxf(0.f, 1 - fabsf(b1 - n2));
+        }
+        if (ok) {
+          const float* vr = vf + (int64_t)hh * rs + (int64_t)ww * g.Fp;
+          float4 A[4], B[4];
+#pragma unroll
+          for (int j = 0; j < 4; j++) A[j] = ldg4(vr + j * g.Fp);
+#pragma unroll
+          for (int pi = 0; pi < 3; pi++) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) B[j] = ldg4(vr + (pi + 1) * rs + j * g.Fp);
+#pragma unroll
+            for (int pj = 0; pj < 3; pj++) {
+              float4 pix = f4zero();   // tap order and weights gh*gw as shared_kernel.cu:738-771
+              axpy4(pix, gh[pi][0] * gw[pj][0], A[pj]); axpy4(pix, gh[pi][0] * gw[pj][1], A[pj + 1]);
+              axpy4(pix, gh[pi][1] * gw[pj][0], B[pj]); axpy4(pix, gh[pi][1] * gw[pj][1], B[pj + 1]);
+              axpy4(acc[pi * 3 + pj], weight, pix);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) A[j] = B[j];
+          }
+        } else if (o.K <= 32) {
+          slow |= 1u << ki;   // deferred: a warp then runs the per-pixel path only as often as its worst lane needs
+        } else {
+          slow_path(weight, n0, c1, c2);
+        }
+      }
+    }
+    while (slow) {
+      const int ki = __ffs(slow) - 1;
+      slow &= slow - 1;
+      const float* f = reinterpret_cast<const float*>(P.flows) + (qb + ki) * 3;
+      float n0 = bnd((float)t + __ldg(f), g.T), c1 = bnd((float)rh + __ldg(f + 1), H), c2 = bnd((float)rw + __ldg(f + 2), W);
+      slow_path(__ldg(P.weights + qb + ki), n0, c1, c2);
+    }
+  }
+  // 9 phases: patch pixel (pi,pj) of every query lands on a different tile pixel
+#pragma unroll
+  for (int pp = 0; pp < 9; pp++) {
+    const int h = rh + pp / 3 + po - h0, w = rw + pp % 3 + po - w0;
+    if (active && h >= 0 && h < C.TH && w >= 0 && w < C.TW) {
+      float4& d = tile[(h * C.TW + w) * Q4 + c4];
+      d.x += acc[pp].x; d.y += acc[pp].y; d.z += acc[pp].z; d.w += acc[pp].w;
+    }
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < C.TH * C.TW * Q4; i += blockDim.x) {
+    const int q4 = i % Q4, px = i / Q4;
+    const int h = h0 + px / C.TW, w = w0 + px % C.TW;
+    if (h >= H || w >= W) continue;
+    const float cnt = (float)(P.counts_h[h] * P.counts_w[w]);
+    const float4 a = tile[i];
+    *reinterpret_cast<float4*>(P.out + ((((int64_t)n * g.Tq + tl) * H + h) * W + w) * g.Fp + q4 * 4) =
+        make_float4(a.x / cnt, a.y / cnt, a.z / cnt, a.w / cnt);
+  }
+}
+
+
 // FAST3: ps == 3 && dilation == 1.  The 9 bilinear reads of one neighbour patch then share a 4x4
 // pixel footprint (all patch pixels have the same fractional position), so an interior (query, k)
 // pair reads 16 value pixels and issues 16 vector REDs instead of 36 + 36.
@@ -334,6 +501,28 @@ static int agg_forward(float* out_cl, const float* v_cl, const float* weights, c
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_forward: too many threads for one launch");
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
   cudaStream_t st = (cudaStream_t)stream;
+  if (!stack && o->ps == 3 && o->dilation == 1 && P.nquad <= 4 && !getenv("STNLS_WPF_NO_TILE")) {
+    // tile: the largest with (queries touching the tile) x quads <= 512 threads
+    static const int dims[5][2] = {{16, 32}, {16, 16}, {12, 16}, {8, 16}, {8, 8}};
+    TileCfg C = {};
+    for (int i = 0; i < 5; i++) {
+      C.TH = dims[i][0]; C.TW = dims[i][1];
+      C.nQh = (C.TH + 1) / o->stride0 + 1; C.nQw = (C.TW + 1) / o->stride0 + 1;
+      if (C.nQh * C.nQw * P.nquad <= 512) break;
+    }
+    const int threads = (C.nQh * C.nQw * P.nquad + 31) / 32 * 32;
+    C.tiles_w = (g->kW + C.TW - 1) / C.TW;
+    const int tiles_h = (g->kH + C.TH - 1) / C.TH;
+    const int64_t ny = (int64_t)g->B * g->HD * g->Tq;
+    if (threads <= 512 && ny <= 65535) {
+      dim3 grid((unsigned)(C.tiles_w * tiles_h), (unsigned)ny);
+      const size_t smem = (size_t)C.TH * C.TW * P.nquad * 16;
+      if (o->itype_int) wpsum_fwd_tile_kernel<true><<<grid, threads, smem, st>>>(P, C);
+      else wpsum_fwd_tile_kernel<false><<<grid, threads, smem, st>>>(P, C);
+      STNLS_CHECK_LAUNCH("wpsum_forward(tile)");
+      return STNLS_OK;
+    }
+  }
   if (o->itype_int) wpsum_fwd_kernel<true><<<blocks, 128, 0, st>>>(P);
   else wpsum_fwd_kernel<false><<<blocks, 128, 0, st>>>(P);
   STNLS_CHECK_LAUNCH("wpsum_forward");

@@ -262,11 +262,15 @@ class ShardedSearchAgg(th.nn.Module):
                 if halo == "peer":
                     raise
 
-    def forward(self, q, k, v, flows):
+    def forward(self, q, k, v, flows, v_ready=None):
+        """v_ready: optional CUDA event after which `v` is valid (e.g. its host->device copy on a side stream);
+        the current stream waits for it only when the aggregation needs v, so the copy overlaps the search."""
         k_ext = halo_exchange(k, self.plan, self.group, self.peer, "k")
-        v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
         dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
         sign = -1.0 if self.search.dist_type == "l2" else 1.0
         weights = softmax_scaled(dists, sign * self.scale)   # fused sign/scale/softmax (normz, SURVEY.md 8f N2)
+        if v_ready is not None:
+            th.cuda.current_stream().wait_event(v_ready)
+        v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
         out = self.agg(v_ext, weights, inds, shard=self.plan.shard)
         return out, dists, inds
