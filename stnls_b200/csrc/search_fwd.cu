@@ -214,6 +214,23 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
     while ((mp & 7) != (wsz & 7)) mp++;
     if (mp <= C.M + 4) C.Mp = mp;
   }
+  // run tiling: candidates wj, wj + rs, wj + 2 rs of one row share lattice columns when n1 divides n2
+  C.tile = 0; C.rs = 1; C.nruns = 0; C.inv_nTg = 0.f;
+  if (ps == 3 && (C.n2 % C.n1) == 0 && wsz <= 64 && !getenv("STNLS_FWD_NO_TILE")) {
+    C.rs = C.n2 / C.n1;
+    for (int rho = 0; rho < C.rs && rho < wsz; rho++) {
+      int members = (wsz - 1 - rho) / C.rs + 1;
+      for (int m0 = 0; m0 < members; m0 += 3) {
+        if (C.nruns >= 32) break;
+        int cnt = members - m0 < 3 ? members - m0 : 3;
+        C.runs[C.nruns++] = (unsigned)((rho + m0 * C.rs) | (cnt << 8));
+      }
+    }
+    int covered = 0;
+    for (int i = 0; i < C.nruns; i++) covered += C.runs[i] >> 8;
+    // enough runs per group to fill a warp's lanes, and the kernel variant that carries the tiled loop
+    if (covered == wsz && (C.Mp & 1) && wsz * C.nruns >= 16 && C.Q4 == 4) { C.tile = 1; C.inv_nTg = 1.f / (wsz * C.nruns); }
+  }
   int want = (C.Q4 == 2) ? 4 : (C.Q4 == 4) ? 2 : (C.Q4 >= 8 ? 1 : 0);
   C.PS4 = C.M * C.Mp;
   if (C.Q4 > 1) while ((C.PS4 & 7) != want) C.PS4++;
@@ -227,8 +244,9 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
   for (int nb = 1; nb <= 8 && nb <= P.nG; nb++) {
     int bytes = nb * C.GS4 * 16;
     if (nb > 1 && bytes > budget) break;
-    int rounds = (nb * P.G + 31) / 32;
-    double eff = (double)(nb * P.G) / (32.0 * rounds);
+    const int units = C.tile ? wsz * C.nruns : P.G;   // lanes of work per group in the candidate phase
+    int rounds = (nb * units + 31) / 32;
+    double eff = (double)(nb * units) / (32.0 * rounds);
     if (eff > best_eff + 0.02) { best_eff = eff; best = nb; }
   }
   C.nb = env_nb ? atoi(env_nb) : best;

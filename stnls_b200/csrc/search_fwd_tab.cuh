@@ -22,6 +22,10 @@ struct TabCfg {
   int D;          // lattice denominator (u = 1/D)
   int W8, nA;     // candidate enumeration: columns [0,W8) row-wise in chunks of 8 (nA = wsz*W8 lanes), rest column-wise
   float inv_W8;
+  // run tiling of the candidate phase (ps == 3, n1 | n2): a lane owns up to 3 candidates wj = w0 + rs*j of a row
+  int tile, rs, nruns;
+  float inv_nTg;
+  unsigned runs[32];  // w0 | count << 8
 };
 
 // one per translation unit; each picks dist_type / ps / channel-quad template variants at run time

@@ -81,7 +81,7 @@ __device__ __forceinline__ float4 lattice_value(const char* kc, const float4 eh,
 
 // PS: patch size (0 = run time); Q4T: channel quads (0 = run time)
 template <bool INT, int DIST, bool REFINE, int PS, int Q4T>
-__global__ void __launch_bounds__(256, (PS * PS * Q4T >= 36 || Q4T == 0) ? 3 : 4) search_fwd_tab_kernel(const __grid_constant__ FwdParams P,
+__global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 3 : 4) search_fwd_tab_kernel(const __grid_constant__ FwdParams P,
                                                                 const __grid_constant__ TabCfg C) {
   typedef typename CT<INT>::type CC;
   extern __shared__ float4 smem4[];
@@ -290,7 +290,126 @@ __global__ void __launch_bounds__(256, (PS * PS * Q4T >= 36 || Q4T == 0) ? 3 : 4
       }
     }
     __syncwarp();
-    // 3. candidates of this batch: lane = candidate
+    // 3. candidates of this batch
+    const unsigned qa = sb + qb * 16, rstep = C.n2 * C.Mp * 16, cstep = C.n2 * 16, pstep = C.PS4 * 16;
+    // distance of one candidate with per-pixel validity masks (frame borders, clipped query patches)
+    auto dist_masked = [&](unsigned Tc, unsigned hm, unsigned wm) {
+      float dist = 0.f;
+      for (int pi = 0; pi < ps; pi++) {
+        if (!((hm >> (C.n2 * pi)) & 1)) continue;
+        for (int pj = 0; pj < ps; pj++) {
+          if (!(((wm >> (C.n2 * pj)) & (qmask >> (pi * ps + pj))) & 1)) continue;
+          const unsigned tp = Tc + pi * rstep + pj * cstep;
+          const unsigned qp = qa + (pi * ps + pj) * Q4 * 16;
+          for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, lds4(qp + c4 * 16), lds4(tp + c4 * pstep));
+        }
+      }
+      return dist;
+    };
+    // anchor swap (an involution; anchor_self_kernel.cu:101-113), slot-0 / keep-all outputs, key of the top-K
+    auto finish = [&](bool active, int gq, const Group<CC>& gp, int ag, int s, float d) {
+      const int pos = gq * P.G + s;
+      int eff = pos;
+      if (anchored) {
+        if (REFINE) { if (s == 0) eff = gq * P.G + ag; else if (s == ag) eff = gq * P.G; }
+        else { if (pos == 0) eff = a_nls; else if (pos == a_nls) eff = 0; }
+      }
+      if (keep_all || (anchored && eff == 0)) {
+        if (active) {
+          const bool to_slot0 = anchored && (REFINE ? (eff % P.G == 0 && ag != 0) : (eff == 0 && a_nls != 0));
+          int64_t oi = obase + (keep_all ? eff : 0);
+          CC ind[3];
+          if (to_slot0) {
+            if (REFINE) refine_loc<CC>(P, c, eff / P.G, ind);
+            else ind[0] = ind[1] = ind[2] = (CC)0;
+          } else cand_inds<CC>(P, c, gp, s, ind);
+          P.dists[oi] = d;
+          inds_out[oi * 3] = ind[0]; inds_out[oi * 3 + 1] = ind[1]; inds_out[oi * 3 + 2] = ind[2];
+          if (P.kselect) P.kselect[oi] = gp.ok ? gq : 1;
+        }
+        if (keep_all) return;
+      }
+      if (active && !(anchored && eff == 0))
+        sts1(sb + (keyb + eff) * 4, min(f2ord(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu));
+    };
+
+    if (PS == 3 && Q4T == 4 && C.tile) {   // 16 channels per head: the variant compiled with the register budget for it
+      // 3a. lane = RUN of up to 3 candidates of one window row whose patches overlap column-wise (candidate
+      // j of the run uses lattice columns c = pj + j of the run's 5): every T value is loaded once for the
+      // run instead of once per candidate (15 instead of 27 LDS.128 per quad) and the query patch row sits
+      // in registers (9 instead of 27 broadcast reads) -- the shared-memory pipe is what bounds this kernel.
+      // Each candidate still accumulates pi -> pj -> channel, so the int path stays bit-exact.
+      constexpr int Q4C = Q4T > 0 ? Q4T : 1;
+      const int nTg = P.wsz * C.nruns, nT = nbg * nTg;
+      for (int base = 0; base < nT; base += 32) {
+        const bool tact = base + lane < nT;
+        const int tb = min(base + lane, nT - 1);
+        const int gl = (C.nb == 1) ? 0 : fdiv(tb, C.inv_nTg);
+        const int e = tb - gl * nTg;
+        const int run = fdiv(e, C.inv_wsz);
+        const int wi = e - run * P.wsz;             // window row fastest: conflict-free T reads (odd row pitch)
+        const unsigned rd = C.runs[run];
+        const int w0 = rd & 255, cnt = rd >> 8;
+        const int gq = g0 + gl;
+        Group<CC> gp = shfl_group(mine, gl);
+        const int ag = (REFINE && anchored) ? __shfl_sync(FULL_MASK, my_ag, gl) : 0;
+        CC chh;
+        if (INT) chh = (CC)((int)gp.ah + (int)s1c * (wi - (int)gp.offh));
+        else chh = (CC)fmaf((float)s1c, (float)wi - (float)gp.offh, (float)gp.ah);
+        const bool rowok = tact && gp.ok && inb(gp.t, g.T) && inb(chh, g.kH);
+        const int mh0 = C.n1 * wi;
+        const unsigned hm = lds1(sb + (mskb + gl * 2) * 4) >> mh0, wmask = lds1(sb + (mskb + gl * 2 + 1) * 4);
+        const bool hfull = qfull && ((hm & C.rpat) == C.rpat);
+        const unsigned Tr = sb + (Tb + gl * C.GS4 + mh0 * C.Mp) * 16;
+        bool cv[3], fastok = true;
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+          const int wj = w0 + C.rs * r;
+          CC cww;
+          if (INT) cww = (CC)((int)gp.aw + (int)s1c * (wj - (int)gp.offw));
+          else cww = (CC)fmaf((float)s1c, (float)wj - (float)gp.offw, (float)gp.aw);
+          cv[r] = rowok && r < cnt && inb(cww, g.kW);
+          const unsigned wm = wmask >> (C.n1 * wj);
+          fastok = fastok && (!cv[r] || (hfull && ((wm & C.rpat) == C.rpat)));
+        }
+        float dr[3] = {invalid, invalid, invalid};
+        if (__all_sync(FULL_MASK, fastok)) {
+          if (cv[0] || cv[1] || cv[2]) {
+            float dist[3] = {0.f, 0.f, 0.f};
+            const unsigned T0 = Tr + C.n1 * w0 * 16;
+#pragma unroll
+            for (int pi = 0; pi < 3; pi++) {
+              float4 qv[3][Q4C];
+#pragma unroll
+              for (int pj = 0; pj < 3; pj++)
+#pragma unroll
+                for (int c4 = 0; c4 < Q4C; c4++) qv[pj][c4] = lds4(qa + ((pi * 3 + pj) * Q4C + c4) * 16);
+#pragma unroll
+              for (int cc = 0; cc < 5; cc++) {
+#pragma unroll
+                for (int c4 = 0; c4 < Q4C; c4++) {
+                  const float4 tv = lds4(T0 + pi * rstep + cc * cstep + c4 * pstep);
+#pragma unroll
+                  for (int j = 0; j < 3; j++)
+                    if (cc - j >= 0 && cc - j < 3) dist[j] = acc4<DIST>(dist[j], qv[cc - j][c4], tv);
+                }
+              }
+            }
+#pragma unroll
+            for (int r = 0; r < 3; r++) if (cv[r]) dr[r] = dist[r];
+          }
+        } else {
+#pragma unroll
+          for (int r = 0; r < 3; r++) {
+            const int wj = w0 + C.rs * r;
+            if (cv[r]) dr[r] = dist_masked(Tr + C.n1 * wj * 16, hm, wmask >> (C.n1 * wj));
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < 3; r++) finish(tact && r < cnt, gq, gp, ag, wi * P.wsz + w0 + C.rs * r, dr[r]);
+      }
+    } else {
+    // 3b. lane = candidate
     const int nC = nbg * P.G;
     for (int base = 0; base < nC; base += 32) {
       const bool active = base + lane < nC;
@@ -306,7 +425,6 @@ __global__ void __launch_bounds__(256, (PS * PS * Q4T >= 36 || Q4T == 0) ? 3 : 4
       else { const int e2 = e - C.nA; const int cc = fdiv(e2, C.inv_wsz); wi = e2 - cc * P.wsz; wj = C.W8 + cc; }
       const int s = wi * P.wsz + wj;
       const int gq = g0 + gl;
-      const int pos = gq * P.G + s;
       Group<CC> gp = shfl_group(mine, gl);
       const int ag = (REFINE && anchored) ? __shfl_sync(FULL_MASK, my_ag, gl) : 0;
       CC chh, cww;
@@ -321,7 +439,6 @@ __global__ void __launch_bounds__(256, (PS * PS * Q4T >= 36 || Q4T == 0) ? 3 : 4
       const int mh0 = C.n1 * wi, mw0 = C.n1 * wj;
       const unsigned hm = lds1(sb + (mskb + gl * 2) * 4) >> mh0, wm = lds1(sb + (mskb + gl * 2 + 1) * 4) >> mw0;
       const unsigned Tc = sb + (Tb + gl * C.GS4 + mh0 * C.Mp + mw0) * 16;
-      const unsigned qa = sb + qb * 16, rstep = C.n2 * C.Mp * 16, cstep = C.n2 * 16, pstep = C.PS4 * 16;
       const bool allpix = qfull && ((hm & C.rpat) == C.rpat) && ((wm & C.rpat) == C.rpat);
       float d = invalid;
       if (__all_sync(FULL_MASK, allpix || !cvalid)) {
@@ -341,41 +458,10 @@ __global__ void __launch_bounds__(256, (PS * PS * Q4T >= 36 || Q4T == 0) ? 3 : 4
           d = dist;
         }
       } else if (cvalid) {
-        float dist = 0.f;
-        for (int pi = 0; pi < ps; pi++) {
-          if (!((hm >> (C.n2 * pi)) & 1)) continue;
-          for (int pj = 0; pj < ps; pj++) {
-            if (!(((wm >> (C.n2 * pj)) & (qmask >> (pi * ps + pj))) & 1)) continue;
-            const unsigned tp = Tc + pi * rstep + pj * cstep;
-            const unsigned qp = qa + (pi * ps + pj) * Q4 * 16;
-            for (int c4 = 0; c4 < Q4; c4++) dist = acc4<DIST>(dist, lds4(qp + c4 * 16), lds4(tp + c4 * pstep));
-          }
-        }
-        d = dist;
+        d = dist_masked(Tc, hm, wm);
       }
-      // position after the anchor swap (an involution; anchor_self_kernel.cu:101-113)
-      int eff = pos;
-      if (anchored) {
-        if (REFINE) { if (s == 0) eff = gq * P.G + ag; else if (s == ag) eff = gq * P.G; }
-        else { if (pos == 0) eff = a_nls; else if (pos == a_nls) eff = 0; }
-      }
-      if (keep_all || (anchored && eff == 0)) {
-        if (active) {
-          const bool to_slot0 = anchored && (REFINE ? (eff % P.G == 0 && ag != 0) : (eff == 0 && a_nls != 0));
-          int64_t oi = obase + (keep_all ? eff : 0);
-          CC ind[3];
-          if (to_slot0) {
-            if (REFINE) refine_loc<CC>(P, c, eff / P.G, ind);
-            else ind[0] = ind[1] = ind[2] = (CC)0;
-          } else cand_inds<CC>(P, c, gp, s, ind);
-          P.dists[oi] = d;
-          inds_out[oi * 3] = ind[0]; inds_out[oi * 3 + 1] = ind[1]; inds_out[oi * 3 + 2] = ind[2];
-          if (P.kselect) P.kselect[oi] = gp.ok ? gq : 1;
-        }
-        if (keep_all) continue;
-      }
-      if (active && !(anchored && eff == 0))
-        sts1(sb + (keyb + eff) * 4, min(f2ord(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu));
+      finish(active, gq, gp, ag, s, d);
+    }
     }
     __syncwarp();
   }
