@@ -8,6 +8,7 @@ direction (csrc/normz.cu) instead of four torch ops.  `softmax_scaled(dists, sca
 import torch as th
 
 from .. import ops
+from ..utils import extract_pairs
 
 
 class _SoftmaxScaled(th.autograd.Function):
@@ -54,6 +55,18 @@ class SoftmaxNormalize(th.nn.Module):
         return weights, inds
 
 
+def default_pairs():
+    """lib/stnls/normz/api.py:42-48"""
+    return {"normz_scale": 10, "normz_name": "softmax", "normz_drop_rate": 0., "dist_type": "l2", "k_agg": -1}
+
+
+def extract_config(cfg, restrict=True):
+    return extract_pairs(cfg, default_pairs(), restrict=restrict)
+
+
 def init(cfg):
-    """lib/stnls/normz/softmax.py:7-8"""
+    """lib/stnls/normz/api.py:24-40 + softmax.py:7-8"""
+    cfg = extract_config(cfg, False)
+    if cfg.normz_name != "softmax":
+        raise NotImplementedError(f"stnls_b200: normalisation [{cfg.normz_name}] (the reference menu has softmax only)")
     return SoftmaxNormalize(cfg.normz_scale, cfg.normz_drop_rate, cfg.dist_type, cfg.k_agg)
