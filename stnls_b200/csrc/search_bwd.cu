@@ -6,6 +6,9 @@
 //   nls_bwd_vid_kernel / nls_bwd_vidflows_kernel lib/csrc/search/non_local_search_bilin2d_kernel.cu:285-371,464-598
 //   refinement_vidflows_backward_kernel        lib/csrc/search/refinement_bilin2d_kernel.cu:359-491
 #include "common.cuh"
+#ifndef SB_MINB
+#define SB_MINB 4
+#endif
 #include <cstdlib>
 
 namespace {
@@ -39,7 +42,7 @@ struct BwdParams {
 // PS > 0: compile-time patch size (grad_q of the patch is kept in registers over the K neighbours)
 // KSPLIT: one thread per (query, neighbour, quad) instead of a loop over the K neighbours
 template <int MODE, int DIST, int PS, bool FAST, bool KSPLIT>
-__global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : 4) search_bwd_kernel(const __grid_constant__ BwdParams P) {
+__global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_bwd_kernel(const __grid_constant__ BwdParams P) {
   const stnls_geom& g = P.g;
   const stnls_search_opts& o = P.o;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

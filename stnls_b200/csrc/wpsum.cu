@@ -8,6 +8,9 @@
 // patch-overlap count fused in.  The backward keeps grad_weights / grad_flows in registers and
 // scatters grad_v with 16-byte vector REDs.
 #include "common.cuh"
+#ifndef WB_MINB
+#define WB_MINB 4
+#endif
 #include <cstdlib>
 
 namespace {
@@ -274,7 +277,7 @@ __global__ void __launch_bounds__(512) wpsum_fwd_tile_kernel(const __grid_consta
 // KSPLIT: one thread per (query, neighbour, quad) instead of a loop over the K neighbours -- K times
 // more threads in flight for a kernel that is latency-bound, not bandwidth-bound
 template <bool INT, bool FAST3, bool KSPLIT>
-__global__ void __launch_bounds__(128, 4) wpsum_bwd_kernel(const __grid_constant__ AggParams P) {
+__global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_constant__ AggParams P) {
   const stnls_geom& g = P.g;
   const stnls_agg_opts& o = P.o;
   const int H = g.kH, W = g.kW;
