@@ -214,6 +214,20 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
     while ((mp & 7) != (wsz & 7)) mp++;
     if (mp <= C.M + 4) C.Mp = mp;
   }
+  // raw mode (see TabCfg): needs the templated kernel variants that carry the code
+  C.raw = 0; C.Mr = C.M + 1; C.Wr = wsz + 1; C.nrr = 0; C.scr_off = 0;
+  C.inv_Mr = 1.f / C.Mr; C.inv_Wr = 1.f / C.Wr; C.inv_nPg = 1.f / (C.Wr * C.Wr); C.inv_nTr = 0.f;
+  if (!o.itype_int && o.dist_type == 0 && D == 1 && C.n1 == 1 && C.n2 == 1 && wsz <= 60 &&
+      ((ps == 1 && (C.Q4 == 2 || C.Q4 == 4)) || (ps == 3 && C.Q4 == 4)) && !getenv("STNLS_FWD_NO_RAW")) {
+    C.raw = 1;
+    if (ps == 1) { C.Mp = C.Mr; while ((C.Mp & 7) != (C.Wr & 7)) C.Mp++; }
+    else C.Mp = C.Mr | 1;
+    for (int w0 = 0; w0 < C.Wr && C.nrr < 16; w0 += 4) {
+      int cnt = C.Wr - w0 < 4 ? C.Wr - w0 : 4;
+      C.rruns[C.nrr++] = (unsigned)(w0 | (cnt << 8));
+    }
+    C.inv_nTr = 1.f / (C.Wr * C.nrr);
+  }
   // run tiling: candidates wj, wj + rs, wj + 2 rs of one row share lattice columns when n1 divides n2
   C.tile = 0; C.rs = 1; C.nruns = 0; C.inv_nTg = 0.f;
   if (ps == 3 && (C.n2 % C.n1) == 0 && wsz <= 64 && !getenv("STNLS_FWD_NO_TILE")) {
@@ -232,7 +246,7 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
     if (covered == wsz && (C.Mp & 1) && wsz * C.nruns >= 16 && C.Q4 == 4) { C.tile = 1; C.inv_nTg = 1.f / (wsz * C.nruns); }
   }
   int want = (C.Q4 == 2) ? 4 : (C.Q4 == 4) ? 2 : (C.Q4 >= 8 ? 1 : 0);
-  C.PS4 = C.M * C.Mp;
+  C.PS4 = (C.raw ? C.Mr : C.M) * C.Mp;
   if (C.Q4 > 1) while ((C.PS4 & 7) != want) C.PS4++;
   C.GS4 = C.PS4 * C.Q4;
   // groups per batch: best lane utilisation of the candidate loop within a per-warp smem budget
@@ -244,7 +258,7 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
   for (int nb = 1; nb <= 8 && nb <= P.nG; nb++) {
     int bytes = nb * C.GS4 * 16;
     if (nb > 1 && bytes > budget) break;
-    const int units = C.tile ? wsz * C.nruns : P.G;   // lanes of work per group in the candidate phase
+    const int units = C.raw ? (ps == 1 ? C.Wr * C.Wr : C.Wr * C.nrr) : C.tile ? wsz * C.nruns : P.G;   // lanes of work per group
     int rounds = (nb * units + 31) / 32;
     double eff = (double)(nb * units) / (32.0 * rounds);
     if (eff > best_eff + 0.02) { best_eff = eff; best = nb; }
@@ -260,13 +274,14 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
   C.key_off = C.msk_off + (3 * C.nb + 3) / 4;
   const int key_f4 = (o.K > 0) ? (P.L + 3) / 4 : 0;
   if (key_f4 * 16 > 16 * 1024) return false;
-  C.warp_f4 = C.key_off + key_f4;
+  C.scr_off = C.key_off + key_f4;
+  C.warp_f4 = C.scr_off + (C.raw ? (C.nb * C.Wr * C.Wr + 3) / 4 : 0);
   const char* env_w = getenv("STNLS_FWD_WARPS");
   C.wpb = env_w ? atoi(env_w) : 8;
   if (C.wpb < 1 || C.wpb > 8) C.wpb = 8;
   // bank-conflict-free candidate order needs an odd lattice step per candidate (and the odd row pitch Mp)
   C.W8 = ((C.n1 & 1) && !getenv("STNLS_FWD_ROWMAJOR")) ? (wsz & ~7) : 0;
-  if (wsz < 8) C.W8 = 0;
+  if (wsz < 8 || !(C.Mp & 1)) C.W8 = 0;
   C.nA = wsz * C.W8;
   C.inv_W8 = C.W8 ? 1.f / C.W8 : 0.f;
   C.inv_G = 1.f / P.G; C.inv_wsz = 1.f / wsz; C.inv_Q4 = 1.f / C.Q4; C.inv_M = 1.f / C.M;

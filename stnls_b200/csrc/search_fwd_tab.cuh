@@ -26,6 +26,13 @@ struct TabCfg {
   int tile, rs, nruns;
   float inv_nTg;
   unsigned runs[32];  // w0 | count << 8
+  // "raw" mode (float, prod, unit lattice: stride1 == 1, dilation == 1; ps 1 or 3): when a whole window is
+  // interior the bilinear interpolation commutes with the patch contraction, so the kernel correlates the
+  // query patch with the RAW key pixels on the (ws+1)^2 integer grid and blends the four neighbouring
+  // correlations per candidate -- no interpolated lattice table is built at all
+  int raw, Mr, Wr, nrr, scr_off;   // Mr = M+1 raw rows/cols, Wr = ws+1 correlation grid, nrr runs per grid row
+  float inv_Mr, inv_Wr, inv_nPg, inv_nTr;
+  unsigned rruns[16];              // runs of up to 4 grid columns: w0 | count << 8
 };
 
 // one per translation unit; each picks dist_type / ps / channel-quad template variants at run time

@@ -215,6 +215,11 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
     int my_ag = 0;
     if (REFINE && anchored) my_ag = refine_group_anchor<CC>(P, c, mine, g0 + min(lane, nbg - 1));
     if (lane < nbg) sts1(sb + (gfrb + lane) * 4, (unsigned)((mine.ok && inb(mine.t, g.T)) ? (mine.t - g.tk0) : -1));
+    // raw mode is taken for this batch when every window in it is interior: valid frame, no reflection,
+    // consecutive in-frame taps and the same interpolation weights at every lattice coordinate
+    constexpr bool RAWOK = !INT && DIST == 0 && Q4T > 0 && (PS == 1 || (PS == 3 && Q4T == 4));
+    bool useraw = RAWOK && C.raw && qfull &&
+                  (__ballot_sync(FULL_MASK, lane >= nbg || (mine.ok && inb(mine.t, g.T))) == FULL_MASK);
     // 1. axis tables: one 32-lane round per group (both axes, M <= 16) or per (group, axis)
     for (int rd = 0; rd < nbg * C.ax_rounds; rd++) {
       int gl, axis, m;
@@ -224,7 +229,7 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
       const int lim = axis ? g.kW : g.kH;
       const int sc = axis ? g.Fp * 4 : rowsc;
       const CC a = axis ? gp.aw : gp.ah, off = axis ? gp.offw : gp.offh;
-      bool pv = false;
+      bool pv = false, reg_e = false;
       int o0 = -1, o1 = -1;
       float w0 = 0.f, w1 = 0.f;
       if (m < M) {
@@ -246,8 +251,16 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
           w1 = v1 ? fmaxf(0.f, 1 - fabsf(t1 - p)) : 0.f;
           o0 = v0 ? t0 * sc : 0;
           o1 = v1 ? t1 * sc : (v0 ? t0 * sc : 0);
+          reg_e = pv && v0 && v1 && (o1 == o0 + sc);
         }
         sts4(sb + (axb + (gl * 2 + axis) * M + m) * 16, make_float4(__int_as_float(o0), __int_as_float(o1), w0, w1));
+      }
+      if (RAWOK && useraw) {   // warp-uniform
+        const int src = (C.ax_rounds == 1) ? (lane & 16) : 0;
+        const int o00 = __shfl_sync(FULL_MASK, o0, src);
+        const float w00 = __shfl_sync(FULL_MASK, w0, src), w10 = __shfl_sync(FULL_MASK, w1, src);
+        const bool ok_e = (m >= M) || (reg_e && o0 == o00 + m * sc && w0 == w00 && w1 == w10);
+        useraw = __ballot_sync(FULL_MASK, ok_e) == FULL_MASK;
       }
       unsigned bal = __ballot_sync(FULL_MASK, pv);
       if (lane == 0) {
@@ -259,6 +272,7 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
     // 2. lattice table: item = (mh, mw, channel quad), quads fastest so a warp reads whole pixels
     const int MM = M * M;
     for (int gl = 0; gl < nbg; gl++) {
+      if (RAWOK && useraw) break;
       const int fr = (int)lds1(sb + (gfrb + gl) * 4);
       if (fr < 0) continue;
       const unsigned Ah = sb + (axb + (gl * 2) * M) * 16, Aw = Ah + M * 16;
@@ -333,7 +347,99 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
         sts1(sb + (keyb + eff) * 4, min(f2ord(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu));
     };
 
-    if (PS == 3 && Q4T == 4 && C.tile) {   // 16 channels per head: the variant compiled with the register budget for it
+    if (RAWOK && useraw) {
+      constexpr int Q4C = Q4T > 0 ? Q4T : 1;
+      const int Mr = C.Mr, Wr = C.Wr, WW = Wr * Wr;
+      const unsigned scr = sb + (Tb + C.scr_off) * 16;
+      const int pixb = g.Fp * 4;
+      // 2r. raw key pixels of the (M+1)^2 footprint, one load each
+      for (int gl = 0; gl < nbg; gl++) {
+        const int fr = (int)lds1(sb + (gfrb + gl) * 4);
+        const unsigned Ah = sb + (axb + (gl * 2) * M) * 16, Aw = Ah + M * 16;
+        const int base = __float_as_int(lds4(Ah).x) + __float_as_int(lds4(Aw).x);
+        const int c4 = lane & (Q4C - 1);
+        const char* kc = reinterpret_cast<const char*>(kbase + (int64_t)fr * kfs) + c4 * 16;
+        const unsigned Tgc = sb + (Tb + gl * C.GS4 + c4 * C.PS4) * 16;
+#pragma unroll 2
+        for (int x = lane / Q4C; x < Mr * Mr; x += 32 / Q4C) {
+          const int mh = fdiv(x, C.inv_Mr), mw = x - mh * Mr;
+          sts4(Tgc + (mh * C.Mp + mw) * 16, ldg4b(kc, (unsigned)(base + mh * rowsc + mw * pixb)));
+        }
+      }
+      __syncwarp();
+      // 3r. correlations of the query patch with the raw pixels on the (ws+1)^2 integer grid
+      if (PS == 1) {
+        const int nPt = nbg * WW;
+        for (int base = 0; base < nPt; base += 32) {
+          const int e = min(base + lane, nPt - 1);
+          const int gl = (C.nb == 1) ? 0 : fdiv(e, C.inv_nPg);
+          const int x = e - gl * WW;
+          const int a = fdiv(x, C.inv_Wr), b = x - a * Wr;
+          const unsigned R = sb + (Tb + gl * C.GS4 + a * C.Mp + b) * 16;
+          float cv = 0.f;
+#pragma unroll
+          for (int c4 = 0; c4 < Q4C; c4++) cv = acc4<DIST>(cv, lds4(qa + c4 * 16), lds4(R + c4 * pstep));
+          if (base + lane < nPt) sts1(scr + e * 4, __float_as_uint(cv));
+        }
+      } else {
+        const int nTg = Wr * C.nrr, nT = nbg * nTg;
+        for (int base = 0; base < nT; base += 32) {
+          const int tb = min(base + lane, nT - 1);
+          const int gl = (C.nb == 1) ? 0 : fdiv(tb, C.inv_nTr);
+          const int e = tb - gl * nTg;
+          const int run = fdiv(e, C.inv_Wr);
+          const int a = e - run * Wr;                     // grid row fastest: conflict-free reads (odd row pitch)
+          const unsigned rd = C.rruns[run];
+          const int w0 = rd & 255, cnt = rd >> 8;
+          const unsigned T0 = sb + (Tb + gl * C.GS4 + a * C.Mp + w0) * 16;
+          float dist[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int pi = 0; pi < 3; pi++) {
+            float4 qv[3][Q4C];
+#pragma unroll
+            for (int pj = 0; pj < 3; pj++)
+#pragma unroll
+              for (int c4 = 0; c4 < Q4C; c4++) qv[pj][c4] = lds4(qa + ((pi * 3 + pj) * Q4C + c4) * 16);
+#pragma unroll
+            for (int cc = 0; cc < 6; cc++) {
+#pragma unroll
+              for (int c4 = 0; c4 < Q4C; c4++) {
+                const float4 tv = lds4(T0 + pi * rstep + cc * 16 + c4 * pstep);
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                  if (cc - j >= 0 && cc - j < 3) dist[j] = acc4<DIST>(dist[j], qv[cc - j][c4], tv);
+              }
+            }
+          }
+          if (base + lane < nT) {
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+              if (j < cnt) sts1(scr + (gl * WW + a * Wr + w0 + j) * 4, __float_as_uint(dist[j]));
+          }
+        }
+      }
+      __syncwarp();
+      // 4r. candidate (wi,wj) = bilinear blend of the four correlations around it (tap order of the reference)
+      const int nC = nbg * P.G;
+      for (int base = 0; base < nC; base += 32) {
+        const bool active = base + lane < nC;
+        const int posb = min(base + lane, nC - 1);
+        const int gl = (C.nb == 1) ? 0 : fdiv(posb, C.inv_G);
+        const int s = posb - gl * P.G;
+        const int wi = fdiv(s, C.inv_wsz), wj = s - wi * P.wsz;
+        Group<CC> gp = shfl_group(mine, gl);
+        const int ag = (REFINE && anchored) ? __shfl_sync(FULL_MASK, my_ag, gl) : 0;
+        const unsigned Ah = sb + (axb + (gl * 2) * M) * 16, Aw = Ah + M * 16;
+        const float4 eh = lds4(Ah), ew = lds4(Aw);
+        const unsigned cb = scr + (gl * WW + wi * Wr + wj) * 4;
+        float d = 0.f;
+        d = fmaf(eh.z * ew.z, __uint_as_float(lds1(cb)), d);
+        d = fmaf(eh.z * ew.w, __uint_as_float(lds1(cb + 4)), d);
+        d = fmaf(eh.w * ew.z, __uint_as_float(lds1(cb + Wr * 4)), d);
+        d = fmaf(eh.w * ew.w, __uint_as_float(lds1(cb + Wr * 4 + 4)), d);
+        finish(active, g0 + gl, gp, ag, s, d);
+      }
+    } else if (PS == 3 && Q4T == 4 && C.tile) {   // 16 channels per head: the variant compiled with the register budget for it
       // 3a. lane = RUN of up to 3 candidates of one window row whose patches overlap column-wise (candidate
       // j of the run uses lattice columns c = pj + j of the run's 5): every T value is loaded once for the
       // run instead of once per candidate (15 instead of 27 LDS.128 per quad) and the query patch row sits
@@ -470,12 +576,21 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
   // -- 4. selection: K rounds of warp-wide min over the keys (ties -> lower candidate index) --
   const int Klist = anchored ? P.Kout - 1 : P.Kout;
   const int start = lane + ((anchored && lane == 0) ? 32 : 0);
-  unsigned bk = 0xffffffffu;
-  int bi = 0x7fffffff;
-  for (int i = start; i < P.L; i += 32) {
-    unsigned kv = lds1(sb + (keyb + i) * 4);
-    if (kv < bk) { bk = kv; bi = i; }
-  }
+  // every lane keeps the best TWO of its keys (index ascending, strict <: ties stay with the lower index); a
+  // lane re-reads its keys only when it has been the warp's winner twice since its last scan
+  unsigned bk, bk2;
+  int bi, bi2;
+  auto scan2 = [&]() {
+    bk = bk2 = 0xffffffffu;
+    bi = bi2 = 0x7fffffff;
+    for (int i = start; i < P.L; i += 32) {
+      const unsigned kv = lds1(sb + (keyb + i) * 4);
+      if (kv < bk) { bk2 = bk; bi2 = bi; bk = kv; bi = i; }
+      else if (kv < bk2) { bk2 = kv; bi2 = i; }
+    }
+  };
+  scan2();
+  bool have2 = true;
   unsigned mykey = 0xffffffffu;
   int mypos = 0x7fffffff;
   for (int kk = 0; kk < Klist; kk++) {
@@ -485,12 +600,8 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
     if (lane == kk) { mykey = m; mypos = widx; }
     if (bi == widx) {
       sts1(sb + (keyb + bi) * 4, 0xffffffffu);
-      bk = 0xffffffffu;
-      bi = 0x7fffffff;
-      for (int i = start; i < P.L; i += 32) {
-        unsigned kv = lds1(sb + (keyb + i) * 4);
-        if (kv < bk) { bk = kv; bi = i; }
-      }
+      if (have2) { bk = bk2; bi = bi2; have2 = false; }
+      else { scan2(); have2 = true; }
     }
   }
 

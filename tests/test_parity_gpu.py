@@ -38,6 +38,15 @@ NLS_CASES = [
          dist_type="l2", self_action="anchor", itype="float", flow="float", nF=4),
     dict(name="rvrt_like", B=1, T=4, F=16, H=24, W=24, HD=4, ws=9, wt=1, ps=1, k=9, stride0=1, stride1=1,
          dist_type="prod", self_action=None, itype="float", flow="float"),
+    # raw mode of the forward (float, prod, stride1 == 1): interior windows skip the interpolated lattice
+    dict(name="raw_ps1_f16", B=1, T=4, F=64, H=40, W=36, HD=4, ws=9, wt=1, ps=1, k=9, stride0=1, stride1=1,
+         dist_type="prod", self_action=None, itype="float", flow="float"),
+    dict(name="raw_ps1_f8_anchor", B=1, T=3, F=16, H=30, W=30, HD=2, ws=5, wt=1, ps=1, k=7, stride0=2, stride1=1,
+         dist_type="prod", self_action="anchor", itype="float", flow="float"),
+    dict(name="raw_ps3_f16", B=1, T=4, F=32, H=40, W=44, HD=2, ws=9, wt=1, ps=3, k=20, stride0=1, stride1=1,
+         dist_type="prod", self_action="anchor", itype="float", flow="float"),
+    dict(name="raw_ps3_f16_keepall", B=1, T=3, F=16, H=24, W=24, HD=1, ws=3, wt=1, ps=3, k=-1, stride0=1, stride1=1,
+         dist_type="prod", self_action=None, itype="float", flow="float"),
     dict(name="big_flows", B=1, T=3, F=4, H=12, W=12, HD=1, ws=5, wt=1, ps=3, k=8, stride0=1, stride1=1,
          dist_type="l2", self_action="anchor", itype="int", flow="int", flow_scale=5),
 ]
@@ -66,7 +75,7 @@ def test_nls_forward(c, cuda, oracle):
 
 BWD_CASES = [c for c in NLS_CASES if c["name"] in
              ("readme_int_l2", "readme_int_prod", "readme_float_l2", "readme_float_prod", "ragged_int",
-              "ragged_float", "dilation_adj", "flows_wt_minus_1", "rvrt_like")]
+              "ragged_float", "dilation_adj", "flows_wt_minus_1", "rvrt_like", "raw_ps1_f16", "raw_ps3_f16")]
 
 
 @pytest.mark.parametrize("flows_grad", [False, True])

@@ -28,6 +28,10 @@ CASES = [
          wt=2, ps=3),
     dict(name="float_prod_1p1", itype="float", dist_type="prod", stride1=1.1, flow="float", self_action=None, ws=3,
          wt=1, ps=3, stride0=2),
+    dict(name="float_prod_raw_ps3", itype="float", dist_type="prod", stride1=1.0, flow="float", self_action="anchor", ws=5,
+         wt=1, ps=3, F=32),
+    dict(name="float_prod_raw_ps1", itype="float", dist_type="prod", stride1=1.0, flow="float", self_action=None, ws=5,
+         wt=1, ps=1, F=32),
     dict(name="float_bigflow", itype="float", dist_type="l2", stride1=1.0, flow="float", self_action="anchor", ws=3,
          wt=1, ps=3, flow_scale=6),
 ]
@@ -35,7 +39,7 @@ B, T, F, H, W, HD, K = 1, 5, 8, 24, 20, 2, 8
 
 
 def inputs(c):
-    q, k, v = make_vids(B, T, F, H, W, seed=61)
+    q, k, v = make_vids(B, T, c.get("F", F), H, W, seed=61)
     s0 = c.get("stride0", 1)
     nH, nW = (H - 1) // s0 + 1, (W - 1) // s0 + 1
     flows = make_flows(B, 1, T, 2 * c["wt"] + 1, nH, nW, c["flow"], seed=62) * c.get("flow_scale", 1)
@@ -87,7 +91,7 @@ def test_reference_backward(c, cuda, oracle, refc):
     r0, r1, rf = refc.search_backward(q.to(cuda), k.to(cuda), flows.to(cuda), gd.to(cuda), gi.to(cuda), i.detach(),
                                       c["wt"], c["ps"], dists=d.detach(), **bkw)
     o0, o1, of = oracle.search_backward(q, k, flows, gd, gi, i.detach().cpu(), c["wt"], c["ps"], **bkw)
-    to5 = lambda g: g.permute(0, 2, 1, 3, 4, 5).reshape(B, T, F, H, W)
+    to5 = lambda g: g.permute(0, 2, 1, 3, 4, 5).reshape(B, T, c.get("F", F), H, W)
     for name, ours, ref_, orc in (("grad_q", qg.grad, r0, o0), ("grad_k", kg.grad, r1, o1)):
         assert_close(orc, ref_, 1e-3, 1e-3, "oracle vs reference " + name)
         assert_close(ours, to5(ref_), 1e-3, 1e-3, "cuda vs reference " + name)
