@@ -284,6 +284,9 @@ bool make_tabcfg(const FwdParams& P, TabCfg& C) {
   if (wsz < 8 || !(C.Mp & 1)) C.W8 = 0;
   C.nA = wsz * C.W8;
   C.inv_W8 = C.W8 ? 1.f / C.W8 : 0.f;
+  C.tA8 = wsz & ~7; C.rA8 = C.Wr & ~7;
+  C.inv_tA8 = C.tA8 ? 1.f / C.tA8 : 0.f; C.inv_trem = (wsz - C.tA8) ? 1.f / (wsz - C.tA8) : 0.f;
+  C.inv_rA8 = C.rA8 ? 1.f / C.rA8 : 0.f; C.inv_rrem = (C.Wr - C.rA8) ? 1.f / (C.Wr - C.rA8) : 0.f;
   C.inv_G = 1.f / P.G; C.inv_wsz = 1.f / wsz; C.inv_Q4 = 1.f / C.Q4; C.inv_M = 1.f / C.M;
   return (size_t)C.warp_f4 * 16 <= 24 * 1024;
 }

@@ -33,6 +33,10 @@ struct TabCfg {
   int raw, Mr, Wr, nrr, scr_off;   // Mr = M+1 raw rows/cols, Wr = ws+1 correlation grid, nrr runs per grid row
   float inv_Mr, inv_Wr, inv_nPg, inv_nTr;
   unsigned rruns[16];              // runs of up to 4 grid columns: w0 | count << 8
+  // lane -> (run, row) of the tiled loops: rows [0,A8) of every run first (A8 = rows & ~7, so an 8-lane LDS.128
+  // wavefront stays inside one run and reads 8 different rows), then the leftover rows
+  int tA8, rA8;
+  float inv_tA8, inv_trem, inv_rA8, inv_rrem;
 };
 
 // one per translation unit; each picks dist_type / ps / channel-quad template variants at run time

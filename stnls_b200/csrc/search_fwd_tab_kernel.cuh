@@ -387,8 +387,9 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
           const int tb = min(base + lane, nT - 1);
           const int gl = (C.nb == 1) ? 0 : fdiv(tb, C.inv_nTr);
           const int e = tb - gl * nTg;
-          const int run = fdiv(e, C.inv_Wr);
-          const int a = e - run * Wr;                     // grid row fastest: conflict-free reads (odd row pitch)
+          int run, a;                                      // grid row fastest: conflict-free reads (odd row pitch)
+          if (e < C.nrr * C.rA8) { run = fdiv(e, C.inv_rA8); a = e - run * C.rA8; }
+          else { const int e2 = e - C.nrr * C.rA8; run = fdiv(e2, C.inv_rrem); a = C.rA8 + e2 - run * (Wr - C.rA8); }
           const unsigned rd = C.rruns[run];
           const int w0 = rd & 255, cnt = rd >> 8;
           const unsigned T0 = sb + (Tb + gl * C.GS4 + a * C.Mp + w0) * 16;
@@ -452,8 +453,9 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
         const int tb = min(base + lane, nT - 1);
         const int gl = (C.nb == 1) ? 0 : fdiv(tb, C.inv_nTg);
         const int e = tb - gl * nTg;
-        const int run = fdiv(e, C.inv_wsz);
-        const int wi = e - run * P.wsz;             // window row fastest: conflict-free T reads (odd row pitch)
+        int run, wi;                                // window row fastest: conflict-free T reads (odd row pitch)
+        if (e < C.nruns * C.tA8) { run = fdiv(e, C.inv_tA8); wi = e - run * C.tA8; }
+        else { const int e2 = e - C.nruns * C.tA8; run = fdiv(e2, C.inv_trem); wi = C.tA8 + e2 - run * (P.wsz - C.tA8); }
         const unsigned rd = C.runs[run];
         const int w0 = rd & 255, cnt = rd >> 8;
         const int gq = g0 + gl;
