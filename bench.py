@@ -249,6 +249,7 @@ def run_product(args):
         step(*[t.detach().clone() for t in resident])
     barrier()
     evs = []
+    host_enqueue = []
     ops.TIMELINE = []
     launches0 = ops.LAUNCHES
     barrier()
@@ -257,7 +258,9 @@ def run_product(args):
             flush.zero_()
             e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
             e0.record()
+            h0 = time.perf_counter()
             step(*fresh[i])
+            host_enqueue.append(time.perf_counter() - h0)
             e1.record()
             evs.append((e0, e1))
         barrier()
@@ -265,6 +268,7 @@ def run_product(args):
     timeline, ops.TIMELINE = ops.TIMELINE, None
     t_ms = sum(a.elapsed_time(b) for a, b in evs)
     if os.environ.get("BENCH_DEBUG"):
+        print(f"[rank {rank}] host enqueue ms per step:", [round(x * 1e3, 3) for x in host_enqueue], file=sys.stderr, flush=True)
         print(f"[rank {rank}] per-step ms:", [round(a.elapsed_time(b), 3) for a, b in evs], file=sys.stderr, flush=True)
     del fresh
 
@@ -275,6 +279,7 @@ def run_product(args):
     d2h = 0
     # copies that the search does not wait for (v, grad_out in; the aggregated video out) run on a side stream
     main, side = th.cuda.current_stream(), th.cuda.Stream()
+    gv_pinned = []
     for i in range(args.warmup + args.steps):
         flush.zero_()
         barrier()
@@ -300,11 +305,29 @@ def run_product(args):
                 outs_host[0].copy_(out.detach(), non_blocking=True)
                 out.record_stream(side)
 
+        # grad_v is complete as soon as the aggregation's backward has run: its download overlaps the search backward
+        gv_host = [None]
+
+        def gv_ready(p):
+            if gv_host[0] is None:
+                gv_host[0] = gv_pinned[0] if gv_pinned else th.empty(p.grad.shape, dtype=p.grad.dtype).pin_memory()
+                if not gv_pinned:
+                    gv_pinned.append(gv_host[0])
+            done = th.cuda.Event()
+            done.record(main)
+            with th.cuda.stream(side):
+                side.wait_event(done)
+                gv_host[0].copy_(p.grad, non_blocking=True)
+                p.grad.record_stream(side)
+
+        dev_in[2].requires_grad_(True)
+        hook = dev_in[2].register_post_accumulate_grad_hook(gv_ready)
         out, loss = step(*dev_in, v_ready=v_ready, after_forward=after_forward)
-        res = [dev_in[0].grad, dev_in[1].grad, dev_in[2].grad] + ([dev_in[3].grad] if flt else [])
+        hook.remove()
+        res = [dev_in[0].grad, dev_in[1].grad] + ([dev_in[3].grad] if flt else [])
         if len(outs_host) == 1:
             outs_host += [th.empty(r.shape, dtype=r.dtype).pin_memory() for r in res]
-            d2h = sum(r.numel() * r.element_size() for r in [out] + res)
+            d2h = sum(r.numel() * r.element_size() for r in [out, dev_in[2].grad] + res)
         for hbuf, r in zip(outs_host[1:], res):
             hbuf.copy_(r, non_blocking=True)
         th.cuda.synchronize()
@@ -471,8 +494,8 @@ def main():
             "e2e": {"value": e2e_val, "unit": "Gcandidates/s", "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"], "ms_per_step": e2e_ms,
                     "what": "pinned host q,k,v,flows,grad_out -> device, fwd+bwd through the Python front end, "
-                            "out + grads of q,k,v,flows back to pinned host; the v/grad_out uploads and the download of out run "
-                            "on a side stream (overlapping search / backward); wall clock"},
+                            "out + grads of q,k,v,flows back to pinned host; the v/grad_out uploads and the downloads of out "
+                            "and grad_v run on a side stream (overlapping search / backward); wall clock"},
             "gpu_launches": r["launches"], "clocks": clocks, "roofline": roofline,
             "roofline_fma": roofline_fma, "kernels": kt}
     if world == 1 and not args.no_cpu_baseline:
