@@ -272,6 +272,73 @@ def run_product(args):
         print(f"[rank {rank}] per-step ms:", [round(a.elapsed_time(b), 3) for a, b in evs], file=sys.stderr, flush=True)
     del fresh
 
+    # ---- value, graph form: the same step captured once in a CUDA graph and replayed ---------------
+    # The eager pass above needs ~1.4 ms of host time to enqueue a 2.5 ms step; on a busy host the GPU then
+    # waits for Python.  A graph replay is one launch per step, so `value` is what the kernels deliver.  The
+    # eager pass stays: its per-launch CUDA events feed the kernel table / roofline.
+    graph_ms, graph_note, per_graph = None, None, 0
+    # N>1: the peer-memory halo exchange alternates between two buffers per tag, so a graph holds TWO steps (the
+    # buffer parity is back where it started after each replay), with the L2 flush between them inside the graph.
+    unit = 1 if world == 1 else 2
+    if args.graph != "off" and args.steps % unit:
+        graph_note = "graph replay needs an even --steps at N>1; eager timing reported"
+    elif args.graph != "off" and world > 1 and model.halo_kind != "peer":
+        graph_note = "graph replay at N>1 is only used with the peer-memory halo exchange; eager timing reported"
+    elif args.graph != "off":
+        try:
+            static = [t.detach().clone() for t in resident]
+            leafs = static[:3] + ([static[3]] if flt else [])
+            for t in leafs:
+                t.requires_grad_(True)
+
+            def fwd_bwd():
+                out, dists, inds = model(static[0], static[1], static[2], static[3])
+                loss = (out * static[4]).sum()
+                return out, th.autograd.grad(loss, leafs)
+
+            def captured():
+                res = fwd_bwd()
+                for _ in range(unit - 1):
+                    flush.zero_()
+                    res = fwd_bwd()
+                return res
+
+            cur, cap = th.cuda.current_stream(), th.cuda.Stream()
+            cap.wait_stream(cur)
+            with th.cuda.stream(cap):
+                for _ in range(2):
+                    captured()
+            cur.wait_stream(cap)
+            barrier()
+            l0 = ops.LAUNCHES
+            cg = th.cuda.CUDAGraph()
+            with th.cuda.graph(cg):
+                graph_out = captured()
+            per_graph = ops.LAUNCHES - l0
+            for _ in range(-(-args.warmup // unit)):
+                cg.replay()
+            barrier()
+            gevs = []
+            with ClockSampler(local) as gclk:
+                for i in range(args.steps // unit):
+                    flush.zero_()
+                    e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
+                    e0.record()
+                    cg.replay()
+                    e1.record()
+                    gevs.append((e0, e1))
+                barrier()
+            graph_ms = sum(a.elapsed_time(b) for a, b in gevs)
+            assert bool(th.isfinite(graph_out[0]).all())
+            if os.environ.get("BENCH_DEBUG"):
+                print(f"[rank {rank}] graph per-step ms:", [round(a.elapsed_time(b), 3) for a, b in gevs], file=sys.stderr, flush=True)
+            clk = gclk
+            del cg, graph_out, static
+        except Exception as exc:  # capture not possible here: the eager number stands
+            graph_note = f"graph capture failed: {type(exc).__name__}: {exc}"[:200]
+            graph_ms = None
+            th.cuda.synchronize()
+
     # ---- e2e: pinned host buffers in, results back to pinned host buffers ----------------------
     outs_host = None
     e2e_s = 0.0
@@ -334,12 +401,19 @@ def run_product(args):
         if i >= args.warmup:
             e2e_s += time.perf_counter() - t0
 
-    tt = th.tensor([t_ms, e2e_s * 1e3], dtype=th.float64, device=dev)
+    tt = th.tensor([t_ms, e2e_s * 1e3, graph_ms if graph_ms is not None else -1.0], dtype=th.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ok = th.tensor([1.0 if graph_ms is not None else 0.0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok[0]) == 0.0:
+            graph_ms = None
     t_ms, e2e_ms = float(tt[0]), float(tt[1])
+    if graph_ms is not None:
+        graph_ms = float(tt[2])
     return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
-                launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h)
+                launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h, graph_ms=graph_ms, graph_note=graph_note,
+                per_graph=per_graph, unit=unit)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -441,6 +515,8 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--halo", default="auto", choices=["auto", "peer", "nccl"])
+    ap.add_argument("--graph", default="auto", choices=["auto", "off"],
+                    help="auto: `value` from CUDA-graph replays of the step when capture works")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup
 
@@ -453,7 +529,9 @@ def main():
         return
     wl, world, steps = r["wl"], r["world"], args.steps
     cands = candidates_per_step(wl, world)
-    ms_per_step = r["t_ms"] / steps
+    eager_ms = r["t_ms"] / steps
+    graphed = r["graph_ms"] is not None
+    ms_per_step = r["graph_ms"] / steps if graphed else eager_ms
     value = cands / (ms_per_step * 1e-3) / 1e9
     e2e_ms = r["e2e_ms"] / steps
     e2e_val = cands / (e2e_ms * 1e-3) / 1e9
@@ -470,7 +548,7 @@ def main():
                 "frac": achieved / peak,
                 "traffic": load_traffic(args.workload, dom) if world == 1 else None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg[dom]["bytes"], "ms_per_launch": kt[dom]["ms_per_launch"],
-                "share_of_step": kt[dom]["ms_per_step"] / ms_per_step}
+                "share_of_step": kt[dom]["ms_per_step"] / eager_ms}
     clocks = r["clocks"]
     mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965
     fma_peak = 148 * 128 * 2 * mhz * 1e6 / 1e12
@@ -496,7 +574,13 @@ def main():
                     "what": "pinned host q,k,v,flows,grad_out -> device, fwd+bwd through the Python front end, "
                             "out + grads of q,k,v,flows back to pinned host; the v/grad_out uploads and the downloads of out "
                             "and grad_v run on a side stream (overlapping search / backward); wall clock"},
-            "gpu_launches": r["launches"], "clocks": clocks, "roofline": roofline,
+            "gpu_launches": r["per_graph"] * (steps // r["unit"]) if graphed else r["launches"],
+            "timing": {"value_from": "cuda graph replay of the step (one launch per step; CUDA events around each replay)"
+                                     if graphed else "eager enqueue through the Python front end",
+                       "ms_per_step_eager": eager_ms, "kernel_nodes_per_graph": r["per_graph"] if graphed else None,
+                       "steps_per_graph": r["unit"] if graphed else None,
+                       "note": r["graph_note"] or "`kernels` and `roofline` come from the eager pass (per-launch CUDA events)"},
+            "clocks": clocks, "roofline": roofline,
             "roofline_fma": roofline_fma, "kernels": kt}
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
