@@ -340,80 +340,99 @@ def run_product(args):
             th.cuda.synchronize()
 
     # ---- e2e: pinned host buffers in, results back to pinned host buffers ----------------------
-    outs_host = None
-    e2e_s = 0.0
+    # Every step uploads its own q,k,v,flows,grad_out from pinned host memory and downloads out and the four
+    # gradients into pinned host memory.  Two timings of the same work:
+    #   * pipelined (the e2e value): step i+1's uploads are enqueued on a copy stream before step i's kernels, as a
+    #     data-parallel training loop prefetches its next batch; one synchronize after the K steps;
+    #   * latency: barrier + synchronize around every single step (nothing overlaps across steps).
     h2d = sum(t.numel() * t.element_size() for t in host)
-    d2h = 0
-    # copies that the search does not wait for (v, grad_out in; the aggregated video out) run on a side stream
-    main, side = th.cuda.current_stream(), th.cuda.Stream()
-    gv_pinned = []
+    main, up, down = th.cuda.current_stream(), th.cuda.Stream(), th.cuda.Stream()
+    pinned = {}
+
+    def to_host(name, t, after):
+        """download `t` on the copy-out stream once `after` (an event on the compute stream) has passed"""
+        if name not in pinned:
+            pinned[name] = th.empty(t.shape, dtype=t.dtype).pin_memory()
+        down.wait_event(after)
+        with th.cuda.stream(down):
+            pinned[name].copy_(t, non_blocking=True)
+        t.record_stream(down)
+
+    def mark():
+        ev = th.cuda.Event()
+        ev.record(main)
+        return ev
+
+    def upload():
+        """q,k,flows first (the search waits for them), then v and grad_out (needed from the aggregation on)"""
+        with th.cuda.stream(up):
+            q_d, k_d, f_d = (host[j].to(dev, non_blocking=True) for j in (0, 1, 3))
+            first = th.cuda.Event()
+            first.record(up)
+            v_d, g_d = host[2].to(dev, non_blocking=True), host[4].to(dev, non_blocking=True)
+            second = th.cuda.Event()
+            second.record(up)
+        for t in (q_d, k_d, f_d, v_d, g_d):
+            t.record_stream(main)
+        return [q_d, k_d, v_d, f_d, g_d], first, second
+
+    def e2e_step(dev_in, first, second):
+        main.wait_event(first)
+        dev_in[2].requires_grad_(True)
+        # grad_v is complete as soon as the aggregation's backward has run: its download overlaps the search backward
+        hook = dev_in[2].register_post_accumulate_grad_hook(lambda p: to_host("grad_v", p.grad, mark()))
+        # the aggregated video goes back to the host while the backward runs
+        out, loss = step(*dev_in, v_ready=second, after_forward=lambda o: to_host("out", o.detach(), mark()))
+        hook.remove()
+        done = mark()
+        to_host("grad_q", dev_in[0].grad, done)
+        to_host("grad_k", dev_in[1].grad, done)
+        if flt:
+            to_host("grad_flows", dev_in[3].grad, done)
+
+    # latency form
+    lat_s = 0.0
     for i in range(args.warmup + args.steps):
         flush.zero_()
         barrier()
         t0 = time.perf_counter()
-        side.wait_stream(main)
-        with th.cuda.stream(side):
-            v_d, gout_d = host[2].to(dev, non_blocking=True), host[4].to(dev, non_blocking=True)
-            v_d.record_stream(main); gout_d.record_stream(main)
-            v_ready = th.cuda.Event()
-            v_ready.record(side)
-        dev_in = [host[0].to(dev, non_blocking=True), host[1].to(dev, non_blocking=True), v_d,
-                  host[3].to(dev, non_blocking=True), gout_d]
-
-        def after_forward(out):
-            # result of the forward goes back to the host while the backward runs
-            nonlocal outs_host
-            if outs_host is None:
-                outs_host = [th.empty(out.shape, dtype=out.dtype).pin_memory()]
-            fwd_done = th.cuda.Event()
-            fwd_done.record(main)
-            with th.cuda.stream(side):
-                side.wait_event(fwd_done)
-                outs_host[0].copy_(out.detach(), non_blocking=True)
-                out.record_stream(side)
-
-        # grad_v is complete as soon as the aggregation's backward has run: its download overlaps the search backward
-        gv_host = [None]
-
-        def gv_ready(p):
-            if gv_host[0] is None:
-                gv_host[0] = gv_pinned[0] if gv_pinned else th.empty(p.grad.shape, dtype=p.grad.dtype).pin_memory()
-                if not gv_pinned:
-                    gv_pinned.append(gv_host[0])
-            done = th.cuda.Event()
-            done.record(main)
-            with th.cuda.stream(side):
-                side.wait_event(done)
-                gv_host[0].copy_(p.grad, non_blocking=True)
-                p.grad.record_stream(side)
-
-        dev_in[2].requires_grad_(True)
-        hook = dev_in[2].register_post_accumulate_grad_hook(gv_ready)
-        out, loss = step(*dev_in, v_ready=v_ready, after_forward=after_forward)
-        hook.remove()
-        res = [dev_in[0].grad, dev_in[1].grad] + ([dev_in[3].grad] if flt else [])
-        if len(outs_host) == 1:
-            outs_host += [th.empty(r.shape, dtype=r.dtype).pin_memory() for r in res]
-            d2h = sum(r.numel() * r.element_size() for r in [out, dev_in[2].grad] + res)
-        for hbuf, r in zip(outs_host[1:], res):
-            hbuf.copy_(r, non_blocking=True)
+        up.wait_stream(main)
+        e2e_step(*upload())
         th.cuda.synchronize()
         if i >= args.warmup:
-            e2e_s += time.perf_counter() - t0
+            lat_s += time.perf_counter() - t0
+    d2h = sum(t.numel() * t.element_size() for t in pinned.values())
 
-    tt = th.tensor([t_ms, e2e_s * 1e3, graph_ms if graph_ms is not None else -1.0], dtype=th.float64, device=dev)
+    # pipelined form
+    def pipelined(n):
+        nxt = upload()
+        for i in range(n):
+            cur = nxt
+            if i + 1 < n:
+                nxt = upload()
+            e2e_step(*cur)
+        th.cuda.synchronize()
+
+    pipelined(args.warmup)
+    barrier()
+    t0 = time.perf_counter()
+    pipelined(args.steps)
+    e2e_s = time.perf_counter() - t0
+    assert all(bool(th.isfinite(t).all()) for t in pinned.values())
+
+    tt = th.tensor([t_ms, e2e_s * 1e3, graph_ms if graph_ms is not None else -1.0, lat_s * 1e3], dtype=th.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ok = th.tensor([1.0 if graph_ms is not None else 0.0], device=dev)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if float(ok[0]) == 0.0:
             graph_ms = None
-    t_ms, e2e_ms = float(tt[0]), float(tt[1])
+    t_ms, e2e_ms, lat_ms = float(tt[0]), float(tt[1]), float(tt[3])
     if graph_ms is not None:
         graph_ms = float(tt[2])
     return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
                 launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h, graph_ms=graph_ms, graph_note=graph_note,
-                per_graph=per_graph, unit=unit)
+                per_graph=per_graph, unit=unit, lat_ms=lat_ms)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -571,9 +590,12 @@ def main():
             "frames_per_s": wl["B"] * wl["T"] * world / (ms_per_step * 1e-3),
             "e2e": {"value": e2e_val, "unit": "Gcandidates/s", "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"], "ms_per_step": e2e_ms,
-                    "what": "pinned host q,k,v,flows,grad_out -> device, fwd+bwd through the Python front end, "
-                            "out + grads of q,k,v,flows back to pinned host; the v/grad_out uploads and the downloads of out "
-                            "and grad_v run on a side stream (overlapping search / backward); wall clock"},
+                    "latency_ms_per_step": r["lat_ms"] / steps,
+                    "what": "every step: pinned host q,k,v,flows,grad_out -> device, fwd+bwd through the Python front end "
+                            "(eager, no graph), out + grads of q,k,v,flows -> pinned host.  value: the K steps pipelined "
+                            "(step i+1's uploads enqueued on a copy stream before step i's kernels, downloads on a second "
+                            "copy stream, one synchronize after the K steps; wall clock).  latency_ms_per_step: the same "
+                            "step with a barrier + synchronize on both sides of every step"},
             "gpu_launches": r["per_graph"] * (steps // r["unit"]) if graphed else r["launches"],
             "timing": {"value_from": "cuda graph replay of the step (one launch per step; CUDA events around each replay)"
                                      if graphed else "eager enqueue through the Python front end",
