@@ -169,6 +169,16 @@ int stnls_softmax_forward(float* weights, const float* dists, int64_t rows, int 
 int stnls_softmax_backward(float* grad_dists, const float* grad_weights, const float* weights,
                            int64_t rows, int K, int Kin, float scale, stnls_stream_t stream);
 
+/* ---- per-frame anchoring of the un-reduced candidate list -----------------------------------------
+ * replaces  stnls.nn.anchor_self_time (lib/stnls/nn/anchor_self.py:69-79 -> anchor_self_time_forward_cuda,
+ * lib/csrc/nn/anchor_self_kernel.cu:187-360), the step behind self_action = "anchor_each" and
+ * "anchor_and_remove_ref_frame" (lib/stnls/search/impl/non_local_search.py:96-110).  In place:
+ *  dists (B,HD,Q,G,S) f32, inds (B,HD,Q,G,S,3) i32|f32 (keep-all output of stnls_search_forward, Q = T*nH*nW,
+ *  G = 2wt+1 or 2wt frame groups, S = ws*ws), flows (B,HD_f,T,nflow,2,nH,nW) of the index type.           */
+int stnls_anchor_self_time(float* dists, void* inds, const void* flows, int B, int HD, int HD_f, int T,
+                           int G, int S, int nflow, int wt, int stride0, int qH, int qW, int kH, int kW,
+                           int itype_int, stnls_stream_t stream);
+
 /* separable patch-overlap counts (host helper, no GPU): counts_h[h] = #{(nh,pi): nh*stride0 +
  * dilation*(pi+patch_offset) == h}; equals what gather_add_forward_kernel counts atomically
  * (lib/csrc/agg/gather_add_kernel.cu:94-97).  Returns the minimum count (0 => reference asserts). */

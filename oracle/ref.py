@@ -105,6 +105,62 @@ def topk(dists, inds, k, anchor, descending):
     return standard_topk(dists, inds, k, descending)
 
 
+def topk_each(dists, inds, k, descending, anchor_self=False):
+    """per-frame-group top-K: dists (...,G,S) inds (...,G,S,3) -> (...,G,K'); lib/stnls/nn/topk.py:226-269"""
+    if k <= 0:
+        return dists, inds
+    if anchor_self:
+        d0, i0 = dists[..., :1], inds[..., :1, :]
+        if k > 1 and dists.shape[-1] > 1:
+            d, i, _ = standard_topk(dists[..., 1:], inds[..., 1:, :], min(k - 1, dists.shape[-1] - 1), descending)
+            return th.cat([d0, d], -1), th.cat([i0, i], -2)
+        return d0, i0
+    d, i, _ = standard_topk(dists, inds, min(k, dists.shape[-1]), descending)
+    return d, i
+
+
+SELF_ACTIONS = (None, "anchor", "anchor_self", "anchor_each", "remove", "remove_ref_frame",
+                "anchor_and_remove_ref_frame")
+
+
+def select(dists, inds, flows_k, k, wt, stride0, shapes, self_action, topk_mode, descending,
+           anchor_all, anchor_time):
+    """Everything after the search kernel: lib/stnls/search/impl/non_local_search.py:88-139.
+    dists (B,HD,Q,W_t,ws,ws), inds (...,3); anchor_all(dists(N,L), inds) and anchor_time(dists(B,HD,Q,G,S), inds,
+    flows) work in place (the C oracle here, the reference's kernels in oracle/ref_cuda.py)."""
+    B, HD, Q, W_t, ws, _ = dists.shape
+    T, nH, nW, qH, qW, kH, kW = shapes
+    assert self_action in SELF_ACTIONS
+    anchor = self_action is not None and "anchor" in self_action
+    dists = dists.reshape(B, HD, Q, W_t, ws * ws).contiguous()
+    inds = inds.reshape(B, HD, Q, W_t, ws * ws, 3).contiguous()
+    if self_action in ("anchor", "anchor_self", "remove"):
+        anchor_all(dists.view(B * HD * Q, -1), inds.view(B * HD * Q, -1, 3))
+    if self_action == "anchor_each":
+        anchor_time(dists, inds, flows_k)
+    elif self_action == "remove":
+        dists = dists.view(B, HD, Q, -1)[..., 1:].contiguous()
+        inds = inds.view(B, HD, Q, -1, 3)[..., 1:, :].contiguous()
+    elif self_action in ("remove_ref_frame", "anchor_and_remove_ref_frame"):
+        assert wt > 0, "Cannot remove ref frame if not searching across time."
+        dists = dists[..., 1:, :].contiguous()
+        inds = inds[..., 1:, :, :].contiguous()
+        if self_action == "anchor_and_remove_ref_frame":
+            anchor_time(dists, inds, flows_k)
+    if topk_mode == "all":
+        dists, inds, _ = topk(dists.reshape(B, HD, Q, -1), inds.reshape(B, HD, Q, -1, 3), k, anchor, descending)
+    elif topk_mode == "each":
+        assert dists.dim() == 5, "topk_mode='each' needs the per-frame layout"
+        dists, inds = topk_each(dists, inds, k, descending, anchor_self=anchor)
+    elif topk_mode == "none":
+        assert k <= 0, "If topk_mode is 'none' then k must be <= 0"
+    else:
+        raise ValueError(f"Unknown topk_mode [{topk_mode}]")
+    dists = dists.reshape(B, HD, T, nH, nW, -1).contiguous()
+    inds = inds.reshape(B, HD, T, nH, nW, -1, 3).contiguous()
+    return dists, inds
+
+
 # ---------------------------------------------------------------------------------------------
 #   NonLocalSearch
 # ---------------------------------------------------------------------------------------------
@@ -112,7 +168,7 @@ def topk(dists, inds, k, anchor, descending):
 def nls_forward(vid0, vid1, flows, ws, wt, ps, k, nheads=1, stride0=1, stride1=1,
                 dist_type="l2", dilation=1, self_action=None, ws_interior=0,
                 reflect_bounds=True, full_ws=True, use_adj=False, off_Hq=0, off_Wq=0,
-                strideQ=None, itype="float", return_full=False):
+                strideQ=None, itype="float", return_full=False, topk_mode="all"):
     """lib/stnls/search/non_local_search.py:33-105 + impl/non_local_search.py:23-140"""
     vid0, vid1 = shape_vid(vid0, nheads), shape_vid(vid1, nheads)
     B, HD, T, F, qH, qW = vid0.shape
@@ -147,17 +203,16 @@ def nls_forward(vid0, vid1, flows, ws, wt, ps, k, nheads=1, stride0=1, stride1=1
     lib().oracle_nls_forward(_p(vid0), _p(vid1), _p(flows_k), _p(dists), _p(inds),
                              ctypes.byref(a), int(itype_int))
     full = (dists.clone(), inds.clone()) if return_full else None
-    assert self_action in (None, "anchor", "anchor_self")
-    anchor = self_action is not None
-    L = W_t * ws * ws
-    dists = dists.view(B, HD, Q, L)
-    inds = inds.view(B, HD, Q, L, 3)
-    if anchor:
-        lib().oracle_anchor_self(_p(dists), _p(inds), ctypes.c_int64(B * HD * Q), L, int(itype_int))
-    dists, inds, _ = topk(dists, inds, k, anchor, descending)
-    Kout = dists.shape[-1]
-    dists = dists.reshape(B, HD, T, nH, nW, Kout).contiguous()
-    inds = inds.reshape(B, HD, T, nH, nW, Kout, 3).contiguous()
+    def anchor_all(d, i):
+        lib().oracle_anchor_self(_p(d), _p(i), ctypes.c_int64(d.shape[0]), d.shape[1], int(itype_int))
+
+    def anchor_time(d, i, f):
+        assert d.is_contiguous() and i.is_contiguous() and f.is_contiguous()
+        lib().oracle_anchor_self_time(_p(d), _p(i), _p(f), B, HD, f.shape[1], f.shape[2], d.shape[3], d.shape[4],
+                                      f.shape[3], wt, stride0, qH, qW, kH, kW, int(itype_int))
+
+    dists, inds = select(dists, inds, flows_k, k, wt, stride0, (T, nH, nW, qH, qW, kH, kW), self_action,
+                         topk_mode, descending, anchor_all, anchor_time)
     if return_full:
         return dists, inds, full
     return dists, inds

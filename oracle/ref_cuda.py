@@ -41,7 +41,8 @@ def _shape(vid, nheads):
 
 def nls_forward(vid0, vid1, flows, ws, wt, ps, k, nheads=1, stride0=1, stride1=1, dist_type="l2",
                 dilation=1, self_action=None, ws_interior=0, reflect_bounds=True, full_ws=True,
-                use_adj=False, off_Hq=0, off_Wq=0, strideQ=None, itype="float", return_full=False):
+                use_adj=False, off_Hq=0, off_Wq=0, strideQ=None, itype="float", return_full=False,
+                topk_mode="all"):
     vid0, vid1 = _shape(vid0, nheads), _shape(vid1, nheads)
     dev = vid0.device
     B, HD, T, F, qH, qW = vid0.shape
@@ -68,17 +69,16 @@ def nls_forward(vid0, vid1, flows, ws, wt, ps, k, nheads=1, stride0=1, stride1=1
                                                float(stride1), dilation, 1, reflect_bounds, full_ws,
                                                patch_offset, off_Hq, off_Wq, dist_type_i)
     full = (dists.clone(), inds.clone()) if return_full else None
-    anchor = self_action is not None
-    L = W_t * ws * ws
-    dists = dists.view(B * HD, Q, L)
-    inds = inds.view(B * HD, Q, L, 3)
-    if anchor:
+    def anchor_all(d, i):
+        d3, i3 = d.view(B * HD, Q, -1), i.view(B * HD, Q, -1, 3)
         order = th.zeros((B * HD, Q), dtype=th.int32, device=dev)
-        mod().anchor_self(dists, inds, order, stride0, nH, nW)
-    dists, inds, _ = cref.topk(dists.view(B, HD, Q, L), inds.view(B, HD, Q, L, 3), k, anchor, descending)
-    Kout = dists.shape[-1]
-    dists = dists.reshape(B, HD, T, nH, nW, Kout).contiguous()
-    inds = inds.reshape(B, HD, T, nH, nW, Kout, 3).contiguous()
+        mod().anchor_self(d3, i3, order, stride0, nH, nW)
+
+    def anchor_time(d, i, f):
+        mod().anchor_self_time(d, i, f, wt, stride0, qH, qW, kH, kW)
+
+    dists, inds = cref.select(dists, inds, flows_k, k, wt, stride0, (T, nH, nW, qH, qW, kH, kW), self_action,
+                              topk_mode, descending, anchor_all, anchor_time)
     if return_full:
         return dists, inds, full
     return dists, inds

@@ -477,6 +477,66 @@ void oracle_anchor_self_refine(float* dists, void* inds_v, const void* flows_v,
   }
 }
 
+/* lib/csrc/nn/anchor_self_kernel.cu:187-307 ; dists (B,HD,Q,G,S), inds (...,3), flows (B,HD_f,T,nflow,2,nH,nW),
+ * Q = T*nH*nW; G = 2wt+1 or 2wt frame groups; st_offset = G - nflow (anchor_self_kernel.cu:327) */
+void oracle_anchor_self_time(float* dists, void* inds_v, const void* flows_v,
+                             int B, int HD, int HD_f, int T, int G, int S, int nflow,
+                             int wt, int stride0, int qH, int qW, int kH, int kW, int itype_int){
+  int* inds_i = (int*)inds_v; float* inds_f = (float*)inds_v;
+  const int* flows_i = (const int*)flows_v; const float* flows_f = (const float*)flows_v;
+  int nH = (kH-1)/stride0+1, nW = (kW-1)/stride0+1, nHW = nH*nW;
+  int Q = T*nHW, st_offset = G - nflow;
+  #pragma omp parallel for collapse(3) schedule(static)
+  for (int b=0; b<B; b++) for (int hd=0; hd<HD; hd++) for (int qi=0; qi<Q; qi++){
+    int hd_f = hd % HD_f;
+    int iloc[3]; pixel_loc(iloc,qi,stride0,nW,nHW,qH,qW);
+    int n_hi = iloc[1]/stride0, n_wi = iloc[2]/stride0;
+    int t_max = time_tmax(iloc[0],T,wt);
+    for (int st=0; st<G; st++){
+      int t_next = iloc[0] + st;
+      t_next = (t_next > t_max) ? t_max - st : t_next;
+      int64_t base = ((((int64_t)b*HD+hd)*Q+qi)*G+st)*S;
+      int64_t fo = 0;
+      if (st >= st_offset)
+        fo = (((((int64_t)b*HD_f+hd_f)*T+iloc[0])*nflow+(st-st_offset))*2)*(int64_t)nHW + (int64_t)n_hi*nW + n_wi;
+      int min_idx = 0; float dmin = 10000;
+      if (itype_int){
+        int loc[3] = {t_next - iloc[0], 0, 0};
+        if (st >= st_offset){
+          loc[1] = bounds_i(iloc[1]+flows_i[fo+nHW],kH)-iloc[1];
+          loc[2] = bounds_i(iloc[2]+flows_i[fo],kW)-iloc[2];
+        }
+        for (int s=0; s<S; s++){
+          int64_t o=(base+s)*3;
+          if (inds_i[o]==loc[0] && inds_i[o+1]==loc[1] && inds_i[o+2]==loc[2]){ min_idx=s; break; }
+        }
+        float tmp=dists[base]; dists[base]=dists[base+min_idx]; dists[base+min_idx]=tmp;
+        int64_t o0=base*3, o1=(base+min_idx)*3;
+        int t[3]={inds_i[o0],inds_i[o0+1],inds_i[o0+2]};
+        for (int ix=0; ix<3; ix++) inds_i[o0+ix]=loc[ix];
+        for (int ix=0; ix<3; ix++) inds_i[o1+ix]=t[ix];
+      }else{
+        float loc[3] = {(float)(t_next - iloc[0]), 0.f, 0.f};
+        if (st >= st_offset){
+          loc[1] = bounds_f(iloc[1]+flows_f[fo+nHW],kH)-iloc[1];
+          loc[2] = bounds_f(iloc[2]+flows_f[fo],kW)-iloc[2];
+        }
+        for (int s=0; s<S; s++){
+          int64_t o=(base+s)*3; float delta=0;
+          for (int ix=0; ix<3; ix++) delta += fabsf(inds_f[o+ix]-loc[ix]);
+          if (delta < 1e-8){ min_idx=s; break; }
+          else if (delta < dmin){ min_idx=s; dmin=delta; }
+        }
+        float tmp=dists[base]; dists[base]=dists[base+min_idx]; dists[base+min_idx]=tmp;
+        int64_t o0=base*3, o1=(base+min_idx)*3;
+        float t[3]={inds_f[o0],inds_f[o0+1],inds_f[o0+2]};
+        for (int ix=0; ix<3; ix++) inds_f[o0+ix]=loc[ix];
+        for (int ix=0; ix<3; ix++) inds_f[o1+ix]=t[ix];
+      }
+    }
+  }
+}
+
 /*
  * Search backward.  mode 0: int   (non_local_search_int_kernel.cu:273-355 + nls_int.cu:88-167)
  *                   mode 1: bilin (non_local_search_bilin2d_kernel.cu:285-371 + nls_bilin2d.cu:95-186)

@@ -36,7 +36,7 @@ EXPORTS = ["stnls_last_error", "stnls_version", "stnls_pack_cl", "stnls_unpack_c
            "stnls_search_forward", "stnls_search_backward", "stnls_wpsum_forward",
            "stnls_wpsum_backward", "stnls_gather_forward", "stnls_gather_backward",
            "stnls_search_flow_forward", "stnls_search_flow_backward",
-           "stnls_softmax_forward", "stnls_softmax_backward",
+           "stnls_softmax_forward", "stnls_softmax_backward", "stnls_anchor_self_time",
            "stnls_overlap_counts", "stnls_add_inplace"]
 
 _lib = None
@@ -70,6 +70,7 @@ def lib():
     L.stnls_search_flow_backward.argtypes = [c_vp] * 6 + [c_int] * 6 + [c_vp]
     L.stnls_softmax_forward.argtypes = [c_vp, c_vp, c_i64, c_int, c_int, c_f32, c_vp]
     L.stnls_softmax_backward.argtypes = [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_f32, c_vp]
+    L.stnls_anchor_self_time.argtypes = [c_vp, c_vp, c_vp] + [c_int] * 14 + [c_vp]
     L.stnls_overlap_counts.argtypes = [c_vp] + [c_int] * 6
     L.stnls_add_inplace.argtypes = [c_vp, c_vp, c_i64, c_vp]
     for name in EXPORTS:

@@ -4,3 +4,18 @@ from .search_flow import run as search_flow  # noqa: F401
 from .search_flow import search_flow_th  # noqa: F401
 from . import non_local_attn  # noqa: F401
 from .non_local_attn import NonLocalAttention  # noqa: F401
+
+
+def anchor_self_time(dists, inds, flows, wt, stride0, qH, qW, kH, kW):
+    """stnls.nn.anchor_self_time (lib/stnls/nn/anchor_self.py:69-79): in place on dists (B,HD,Q,W_t,ws,ws) /
+    inds (...,3) (or the flattened (B,HD,Q,W_t,ws*ws) form), flows (B,HD_f,T,W_t[-1],2,nH,nW)."""
+    from .. import ops
+    B, HD, Q, G = dists.shape[:4]
+    ops.anchor_self_time(dists.view(B, HD, Q, G, -1), inds.view(B, HD, Q, G, -1, 3), flows.contiguous(), wt, stride0,
+                         qH, qW, kH, kW)
+
+
+def topk_each(dists, inds, k, descending, anchor_self=False):
+    """stnls.nn.topk_each (lib/stnls/nn/topk.py:226-269), stable."""
+    from ..search.non_local_search import topk_each as impl
+    return impl(dists, inds, k, descending, anchor_self=anchor_self)

@@ -151,6 +151,17 @@ def search_backward(q_cl, k_cl, flows, grad_dists, grad_inds, inds, kselect, ref
     return gq, gk, gflows
 
 
+def anchor_self_time(dists, inds, flows, wt, stride0, qH, qW, kH, kW):
+    """In place on dists (B,HD,Q,G,S) / inds (B,HD,Q,G,S,3); flows (B,HD_f,T,nflow,2,nH,nW) of inds' dtype."""
+    _need_cuda(dists, inds, flows)
+    assert dists.is_contiguous() and inds.is_contiguous() and flows.is_contiguous() and flows.dtype == inds.dtype
+    B, HD, Q, G, S = dists.shape
+    _launch("anchor_self_time", _C.lib().stnls_anchor_self_time, _ptr(dists), _ptr(inds), _ptr(flows), B, HD,
+            flows.shape[1], flows.shape[2], G, S, flows.shape[3], wt, stride0, qH, qW, kH, kW,
+            int(inds.dtype == th.int32), _stream())
+    return dists, inds
+
+
 _COUNT_CACHE = {}
 
 

@@ -8,8 +8,11 @@ Differences that are visible to a caller (all documented in DESIGN.md):
     with a stable torch sort);
   * ties between *exactly equal* distances break towards the lower candidate index (the reference
     uses an unstable argsort, lib/stnls/nn/topk.py:209);
-  * pt != 1, topk_mode != "all", normalize_bwd=True, ws_interior != ws and the self_action values
-    other than None / "anchor" / "anchor_self" raise NotImplementedError.
+  * the other members of the reference's menus -- self_action "anchor_each" / "remove" / "remove_ref_frame" /
+    "anchor_and_remove_ref_frame", topk_mode "each" / "none" -- run the forward kernel in keep-all mode and
+    then follow impl/non_local_search.py:88-139 step by step (per-frame anchoring is the kernel in
+    csrc/anchor.cu, the selections are stable torch sorts, as in lib/stnls/nn/topk.py);
+  * pt != 1, normalize_bwd=True and ws_interior != ws raise NotImplementedError.
 """
 import torch as th
 
@@ -41,12 +44,71 @@ def topk_fallback(dists, inds, k, anchor, descending, extra=None):
     return d.contiguous(), i.contiguous(), (None if e is None else e.contiguous())
 
 
-def check_common(pt, topk_mode, self_action, normalize_bwd, dist_type, itype):
+SELF_ACTIONS = (None, "anchor", "anchor_self", "anchor_each", "remove", "remove_ref_frame",
+                "anchor_and_remove_ref_frame")  # impl/non_local_search.py:90-91
+FUSED_ACTIONS = (None, "anchor", "anchor_self")
+
+
+def topk_each(dists, inds, k, descending, anchor_self=False):
+    """Per-frame-group top-K over (...,G,S) / (...,G,S,3); lib/stnls/nn/topk.py:226-269 (stable sort)."""
+    def std(d, i, K):
+        order = th.sort(d, dim=-1, descending=descending, stable=True)[1][..., :K]
+        return th.gather(d, -1, order), th.gather(i, -2, order[..., None].expand(*order.shape, 3))
+    if k <= 0:
+        return dists, inds
+    if anchor_self:
+        d0, i0 = dists[..., :1], inds[..., :1, :]
+        if k > 1 and dists.shape[-1] > 1:
+            d, i = std(dists[..., 1:], inds[..., 1:, :], k - 1)
+            return th.cat([d0, d], -1), th.cat([i0, i], -2)
+        return d0, i0
+    return std(dists, inds, k)
+
+
+def select_unfused(dists, inds, flows_k, k, ws, wt, stride0, sizes, self_action, topk_mode, descending):
+    """impl/non_local_search.py:88-139 on the keep-all output of the forward kernel (dists (B,HD,T,nH,nW,L) with
+    the whole-list anchor swap already applied for "anchor" / "anchor_self" / "remove")."""
+    qH, qW, kH, kW = sizes
+    B, HD, T, nH, nW, L = dists.shape
+    Q, S = T * nH * nW, ws * ws
+    anchor = self_action is not None and "anchor" in self_action
+    dists = dists.view(B, HD, Q, L // S, S)
+    inds = inds.view(B, HD, Q, L // S, S, 3)
+    if self_action == "anchor_each":
+        ops.anchor_self_time(dists, inds, flows_k, wt, stride0, qH, qW, kH, kW)
+    elif self_action == "remove":
+        dists = dists.view(B, HD, Q, L)[..., 1:].contiguous()
+        inds = inds.view(B, HD, Q, L, 3)[..., 1:, :].contiguous()
+    elif self_action in ("remove_ref_frame", "anchor_and_remove_ref_frame"):
+        assert wt > 0, "Cannot remove ref frame if not searching across time."
+        dists = dists[..., 1:, :].contiguous()
+        inds = inds[..., 1:, :, :].contiguous()
+        if self_action == "anchor_and_remove_ref_frame":
+            ops.anchor_self_time(dists, inds, flows_k, wt, stride0, qH, qW, kH, kW)
+    if topk_mode == "all":
+        if k > 0:
+            dists, inds, _ = topk_fallback(dists.reshape(B, HD, Q, -1), inds.reshape(B, HD, Q, -1, 3), k, anchor,
+                                           descending)
+    elif topk_mode == "each":
+        if dists.dim() != 5:
+            raise ValueError("topk_mode='each' needs the per-frame candidate layout (not self_action='remove')")
+        dists, inds = topk_each(dists, inds, k, descending, anchor_self=anchor)
+    else:  # "none"
+        assert k <= 0, "If topk_mode is 'none' then k must be <= 0"
+    return dists.reshape(B, HD, T, nH, nW, -1).contiguous(), inds.reshape(B, HD, T, nH, nW, -1, 3).contiguous()
+
+
+def check_common(pt, topk_mode, self_action, normalize_bwd, dist_type, itype, nls=False):
     if pt != 1:
         raise NotImplementedError("stnls_b200: pt must be 1 (the reference backward asserts the same)")
-    if topk_mode != "all":
+    if nls:
+        if topk_mode not in ("all", "each", "none"):
+            raise ValueError(f"Unknown topk_mode [{topk_mode}]")
+        if self_action not in SELF_ACTIONS:
+            raise ValueError(f"Uknown option for self_action [{self_action}]")
+    elif topk_mode != "all":
         raise NotImplementedError("stnls_b200: only topk_mode='all' is implemented")
-    if self_action not in (None, "anchor", "anchor_self"):
+    elif self_action not in FUSED_ACTIONS:
         raise NotImplementedError(f"stnls_b200: self_action [{self_action}] is not implemented")
     if normalize_bwd:
         raise NotImplementedError("stnls_b200: normalize_bwd=True is not implemented")
@@ -70,7 +132,7 @@ class NonLocalSearchFunction(th.autograd.Function):
                 dist_type="l2", dilation=1, pt=1, topk_mode="all", self_action=None, ws_interior=0,
                 reflect_bounds=True, full_ws=True, use_adj=False, normalize_bwd=False, k_agg=-1,
                 off_Hq=0, off_Wq=0, itype="float", shard=None):
-        check_common(pt, topk_mode, self_action, normalize_bwd, dist_type, itype)
+        check_common(pt, topk_mode, self_action, normalize_bwd, dist_type, itype, nls=True)
         if ws_interior > 0 and ws_interior != ws:
             raise NotImplementedError("stnls_b200: ws_interior != ws is not implemented")
         in_dim, flow_ndim = vid0.dim(), flows.dim()
@@ -94,7 +156,10 @@ class NonLocalSearchFunction(th.autograd.Function):
         msg = "flows.shape: " + str(flows.shape) + " W_t: " + str(W_t)
         assert flows.shape[3] in [W_t - 1, W_t], msg
         dist_type_i, descending = DIST_MENU[dist_type]
-        anchor = self_action is not None
+        plain = topk_mode == "all" and self_action in FUSED_ACTIONS
+        if not plain and shard is not None:
+            raise NotImplementedError("stnls_b200: frame shards support topk_mode='all' with self_action None/'anchor'")
+        anchor = self_action in ("anchor", "anchor_self", "remove")  # whole-list swap (nn.anchor_self), in the kernel
         if itype == "int":
             flows_k = flows.round().int() if flows.dtype != th.int32 else flows
             stride1_k = float(max(1, int(stride1)))
@@ -105,14 +170,17 @@ class NonLocalSearchFunction(th.autograd.Function):
             strideQ_k = stride0
         flows_k = flows_k.contiguous()
         L = W_t * ws * ws
-        fused = (k <= 0) or (min(k, L) - (1 if anchor else 0) <= ops.MAX_FUSED_K)
+        fused = plain and ((k <= 0) or (min(k, L) - (1 if anchor else 0) <= ops.MAX_FUSED_K))
         geom = ops.make_geom(B, HD, T, F, qH, qW, kH, kW, stride0, tq0, Tq, tk0, Tk)
         opts = SearchOpts(ws, wt, 0, 0, ps, k if fused else -1, stride0, strideQ_k, dilation, stride1_k,
                           int(reflect_bounds), int(full_ws), 0 if use_adj else -(ps // 2), off_Hq, off_Wq,
                           dist_type_i, int(itype == "int"), int(anchor), flows_k.shape[1],
                           W_t - flows_k.shape[3])
         dists, inds, _, _ = ops.search_forward(q_cl, k_cl, flows_k, geom, opts)
-        if not fused:
+        if not plain:
+            dists, inds = select_unfused(dists, inds, flows_k, k, ws, wt, stride0, (qH, qW, kH, kW), self_action,
+                                         topk_mode, descending)
+        elif not fused:
             dists, inds, _ = topk_fallback(dists, inds, k, anchor, descending)
 
         ctx.save_for_backward(q_cl, k_cl, inds, flows_k if itype == "float" else None)

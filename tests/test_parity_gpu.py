@@ -73,6 +73,56 @@ def test_nls_forward(c, cuda, oracle):
     assert_topk_equal(d, i, d_ref, i_ref, exact=(c["itype"] == "int"), what=c["name"])
 
 
+# the rest of the reference's self_action / topk_mode menus (impl/non_local_search.py:88-139): keep-all kernel +
+# per-frame anchoring kernel (csrc/anchor.cu) + stable selections
+MENU = [("anchor_each", "all"), ("anchor_each", "each"), ("remove", "all"), ("remove_ref_frame", "all"),
+        ("remove_ref_frame", "each"), ("anchor_and_remove_ref_frame", "all"), ("anchor_and_remove_ref_frame", "each"),
+        (None, "each"), ("anchor", "each"), (None, "none"), ("anchor_each", "none")]
+
+
+def menu_case(itype, nF=None):
+    c = dict(name="menu", B=1, T=4, F=8, H=18, W=14, HD=2, ws=3, wt=1, ps=3, k=4, stride0=1,
+             stride1=1 if itype == "int" else 0.5, dist_type="l2", self_action=None, itype=itype, flow=itype,
+             flow_scale=2)
+    if nF is not None:
+        c["nF"] = nF
+    return c
+
+
+@pytest.mark.parametrize("nF", [3, 2])
+@pytest.mark.parametrize("itype", ["int", "float"])
+@pytest.mark.parametrize("self_action,topk_mode", MENU, ids=[f"{a}-{m}" for a, m in MENU])
+def test_nls_menu_forward(self_action, topk_mode, itype, nF, cuda, oracle):
+    c = menu_case(itype, nF)
+    q, k, v, flows, kw = build_case(c)
+    kw["self_action"] = self_action
+    kk = -1 if topk_mode == "none" else c["k"]
+    d_ref, i_ref = oracle.nls_forward(q, k, flows, c["ws"], c["wt"], c["ps"], kk, topk_mode=topk_mode, **kw)
+    search = stnls_b200.search.NonLocalSearch(c["ws"], c["wt"], c["ps"], kk, topk_mode=topk_mode, **kw)
+    d, i = search(q.to(cuda), k.to(cuda), flows.to(cuda))
+    assert_topk_equal(d, i, d_ref, i_ref, exact=(itype == "int"), what=f"{self_action}/{topk_mode}/{itype}")
+
+
+@pytest.mark.parametrize("itype", ["int", "float"])
+@pytest.mark.parametrize("self_action,topk_mode", [("anchor_each", "each"), ("remove_ref_frame", "all"), ("remove", "all")])
+def test_nls_menu_backward(self_action, topk_mode, itype, cuda, oracle):
+    c = menu_case(itype)
+    q, k, v, flows, kw = build_case(c)
+    kw["self_action"] = self_action
+    search = stnls_b200.search.NonLocalSearch(c["ws"], c["wt"], c["ps"], c["k"], topk_mode=topk_mode, **kw)
+    qg, kg = q.to(cuda).requires_grad_(True), k.to(cuda).requires_grad_(True)
+    d, i = search(qg, kg, flows.to(cuda))
+    gd = th.randn(d.shape, generator=th.Generator().manual_seed(12))
+    gd = th.where(th.isfinite(d.detach().cpu()), gd, th.zeros_like(gd))
+    (d * gd.to(cuda)).sum().backward()
+    g0, g1, _ = oracle.search_backward(q, k, flows, gd, th.zeros(i.shape), i.detach().cpu(), c["wt"], c["ps"],
+                                       nheads=c["HD"], stride0=c["stride0"], dist_type=c["dist_type"], itype=itype)
+    B, T, F, H, W = q.shape
+    to5 = lambda g: g.permute(0, 2, 1, 3, 4, 5).reshape(B, T, F, H, W)
+    assert_close(qg.grad, to5(g0), 1e-3, 1e-3, "menu grad_q")
+    assert_close(kg.grad, to5(g1), 1e-3, 1e-3, "menu grad_k")
+
+
 BWD_CASES = [c for c in NLS_CASES if c["name"] in
              ("readme_int_l2", "readme_int_prod", "readme_float_l2", "readme_float_prod", "ragged_int",
               "ragged_float", "dilation_adj", "flows_wt_minus_1", "rvrt_like", "raw_ps1_f16", "raw_ps3_f16")]
@@ -300,3 +350,60 @@ def test_layout_roundtrip_and_errors(cuda):
         stnls_b200.search.NonLocalSearch(3, 0, 1, 1, pt=2)(x, x)
     with pytest.raises(AssertionError):
         stnls_b200.search.NonLocalSearch(3, 2, 1, 1, nheads=4)(x, x)  # T=3 < W_t=5
+
+
+@pytest.mark.parametrize("dist_type", ["l2", "prod"])
+@pytest.mark.parametrize("stride1", [1.0, 0.5])
+def test_fwd_anchor_properties(stride1, dist_type, cuda):
+    """The reference's own anchoring test (tests/search/test_non_local_search_bilin2d.py:519-667, test_fwd_anchor):
+    with topk_mode="each", slot 0 of every frame group of "anchor_each" is the candidate the flow points at --
+    the window centre of an un-recentred (full_ws=False) keep-all search -- whatever k and full_ws are; group 0
+    agrees with "anchor"; "anchor_and_remove_ref_frame" gives the same anchors for the non-reference frames."""
+    ws, wt, ps, stride0, HD = 3, 1, 3, 1, 1
+    B, T, F, H, W = 1, 5, 8, 32, 32
+    W_t = 2 * wt + 1
+    gen = th.Generator().manual_seed(123)
+    vid0 = (th.rand((B, T, F, H, W), generator=gen) - 0.5).to(cuda)
+    vid1 = (th.rand((B, T, F, H, W), generator=gen) - 0.5).to(cuda)
+    nH, nW = (H - 1) // stride0 + 1, (W - 1) // stride0 + 1
+    flows = (2 * th.rand((B, T, W_t - 1, 2, nH, nW), generator=gen)).to(cuda)
+
+    def run(k, full_ws, self_action, topk_mode="each"):
+        s = stnls_b200.search.NonLocalSearch(ws, wt, ps, k, HD, stride0=stride0, stride1=stride1, full_ws=full_ws,
+                                             self_action=self_action, dist_type=dist_type, topk_mode=topk_mode,
+                                             itype="float")
+        return s(vid0, vid1, flows)
+
+    vshape = (B, HD, T, nH, nW, W_t)
+    d0, i0 = run(-1, False, None)
+    d0 = d0.view(vshape + (ws * ws,))[..., ws // 2 * ws + ws // 2]
+    i0 = i0.view(vshape + (ws * ws, 3))[..., ws // 2 * ws + ws // 2, :]
+    firsts = [(d0, i0)]
+    for k, full_ws in ((3, False), (5, True)):
+        d, i = run(k, full_ws, "anchor_each")
+        firsts.append((d.view(vshape + (k,))[..., 0], i.view(vshape + (k, 3))[..., 0, :]))
+    for a in range(3):
+        for b in range(a + 1, 3):
+            assert th.allclose(firsts[a][0], firsts[b][0], 1e-3, 1e-3, equal_nan=True)
+            assert th.allclose(firsts[a][1], firsts[b][1], 1e-3, 1e-3, equal_nan=True)
+    d3, i3 = run(8, True, "anchor")
+    d3, i3 = d3.view(vshape + (8,))[..., 0], i3.view(vshape + (8, 3))[..., 0, :]
+    for d, i in firsts:
+        assert th.allclose(d[..., 0], d3[..., 0], 1e-3, 1e-3, equal_nan=True)
+        assert th.allclose(i[..., 0, :], i3[..., 0, :], 1e-3, 1e-3, equal_nan=True)
+    d4, i4 = run(8, True, "anchor_and_remove_ref_frame")
+    d4 = d4.view((B, HD, T, nH, nW, W_t - 1, 8))[..., 0]
+    i4 = i4.view((B, HD, T, nH, nW, W_t - 1, 8, 3))[..., 0, :]
+    # spatial part of the anchors of the non-reference frames: reflect(ref + flow) - ref
+    assert th.allclose(i4[..., 1:], firsts[2][1][..., 1:, 1:], 1e-3, 1e-3)
+    assert th.allclose(d4, firsts[2][0][..., 1:], 1e-3, 1e-3)
+    # anchors equal the reflected flow target
+    grid_h = th.arange(nH, device=cuda).view(1, 1, nH, 1) * stride0
+    grid_w = th.arange(nW, device=cuda).view(1, 1, 1, nW) * stride0
+    for si in range(1, W_t):
+        fh, fw = flows[:, :, si - 1, 1] + grid_h, flows[:, :, si - 1, 0] + grid_w
+        fh = th.where(fh > H - 1, 2 * (H - 1) - fh, fh).abs()
+        fw = th.where(fw > W - 1, 2 * (W - 1) - fw, fw).abs()
+        got = firsts[2][1][:, 0, :, :, :, si]
+        assert th.allclose(got[..., 1], fh - grid_h, 1e-3, 1e-3)
+        assert th.allclose(got[..., 2], fw - grid_w, 1e-3, 1e-3)

@@ -71,6 +71,29 @@ def test_reference_vs_oracle_vs_cuda_forward(c, cuda, oracle, refc):
     assert_topk_equal(d, i, dr, ir, exact=exact, what="cuda vs reference top-K")
 
 
+MENU = [("anchor_each", "all"), ("anchor_each", "each"), ("remove", "all"), ("remove_ref_frame", "each"),
+        ("anchor_and_remove_ref_frame", "all"), ("anchor", "each"), (None, "none")]
+
+
+@pytest.mark.parametrize("itype", ["int", "float"])
+@pytest.mark.parametrize("self_action,topk_mode", MENU, ids=[f"{a}-{m}" for a, m in MENU])
+def test_reference_menu(self_action, topk_mode, itype, cuda, oracle, refc):
+    """self_action / topk_mode menus: the reference's own anchor_self_time / anchor_self kernels + selections
+    (oracle/ref_cuda.py) against the oracle and against the CUDA path."""
+    c = dict(CASES[0] if itype == "int" else CASES[3], ws=3, wt=1, flow_scale=2)
+    q, k, v, flows, kw = inputs(c)
+    kw["self_action"] = self_action
+    kk = -1 if topk_mode == "none" else 4
+    exact = itype == "int"
+    dr, ir = refc.nls_forward(q.to(cuda), k.to(cuda), flows.to(cuda), c["ws"], c["wt"], c["ps"], kk,
+                              topk_mode=topk_mode, **kw)
+    do, io = oracle.nls_forward(q, k, flows, c["ws"], c["wt"], c["ps"], kk, topk_mode=topk_mode, **kw)
+    assert_topk_equal(do, io, dr, ir, exact=exact, what="oracle vs reference")
+    search = stnls_b200.search.NonLocalSearch(c["ws"], c["wt"], c["ps"], kk, topk_mode=topk_mode, **kw)
+    d, i = search(q.to(cuda), k.to(cuda), flows.to(cuda))
+    assert_topk_equal(d, i, dr, ir, exact=exact, what="cuda vs reference")
+
+
 @pytest.mark.parametrize("c", CASES, ids=[c["name"] for c in CASES])
 def test_reference_backward(c, cuda, oracle, refc):
     q, k, v, flows, kw = inputs(c)
