@@ -270,7 +270,7 @@ def search_backward(vid0, vid1, flows, grad_dists, grad_inds, inds, wt, ps, nhea
 def refine_forward(vid0, vid1, flows, ws, wt, wr, k, kr, ps, nheads=1, stride0=4, stride1=1,
                    strideQ=None, dilation=1, dist_type="l2", restricted_radius=True,
                    reflect_bounds=True, full_ws=True, self_action=None, use_adj=False,
-                   off_Hq=0, off_Wq=0, itype="float"):
+                   off_Hq=0, off_Wq=0, itype="float", topk_mode="all"):
     """lib/stnls/search/refinement.py:32-101 + impl/refinement.py:18-112"""
     vid0, vid1 = shape_vid(vid0, nheads), shape_vid(vid1, nheads)
     B, HD, T, F, qH, qW = vid0.shape
@@ -315,14 +315,24 @@ def refine_forward(vid0, vid1, flows, ws, wt, wr, k, kr, ps, nheads=1, stride0=4
         lib().oracle_anchor_self_refine(_p(dists), _p(inds), _p(flows_k), B, HD, flows_k.shape[1],
                                         Q, Ks, wr * wr, stride0, qH, qW, kH, kW, int(itype_int))
     L = Ks * wr * wr
-    dists = dists.view(B, HD, Q, L)
-    inds = inds.view(B, HD, Q, L, 3)
-    dists, inds, order = topk(dists, inds, k, anchor, descending)
-    if kselect is not None:
-        kselect = kselect.view(B, HD, Q, L)
-        if order is not None:
-            kselect = th.gather(kselect, -1, order)
-        kselect = kselect.reshape(B, HD, T, nH, nW, -1).contiguous()
+    assert self_action in (None, "anchor", "anchor_self", "anchor_each")  # impl/refinement.py:83
+    if topk_mode == "each":  # impl/refinement.py:99-106: top-k inside every group of wr*wr candidates
+        dists, inds = topk_each(dists.view(B, HD, Q, Ks, wr * wr), inds.view(B, HD, Q, Ks, wr * wr, 3), k,
+                                descending, anchor_self=anchor)
+        if kselect is not None:  # "all same across dim": every entry of a group carries the group index
+            kselect = kselect.view(B, HD, Q, Ks, wr * wr)[..., :dists.shape[-1]]
+            kselect = kselect.reshape(B, HD, T, nH, nW, -1).contiguous()
+    else:
+        assert topk_mode == "all", f"Unknown topk_mode [{topk_mode}]"
+        dists = dists.view(B, HD, Q, L)
+        inds = inds.view(B, HD, Q, L, 3)
+        dists, inds, order = topk(dists, inds, k, anchor, descending)
+        if kselect is not None:
+            kselect = kselect.view(B, HD, Q, L)
+            if order is not None:
+                kselect = th.gather(kselect, -1, order)
+            kselect = kselect.reshape(B, HD, T, nH, nW, -1).contiguous()
+    dists, inds = dists.reshape(B, HD, Q, -1), inds.reshape(B, HD, Q, -1, 3)
     Kout = dists.shape[-1]
     dists = dists.reshape(B, HD, T, nH, nW, Kout).contiguous()
     inds = inds.reshape(B, HD, T, nH, nW, Kout, 3).contiguous()

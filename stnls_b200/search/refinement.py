@@ -9,7 +9,7 @@ import torch as th
 from .. import ops
 from .._C import SearchOpts
 from ..utils import extract_pairs
-from .non_local_search import DIST_MENU, check_common, shard_of, topk_fallback
+from .non_local_search import DIST_MENU, check_common, shard_of, topk_each, topk_fallback
 
 
 def filter_k(inds, kr):
@@ -33,7 +33,12 @@ class RefineSearchFunction(th.autograd.Function):
                 strideQ=None, dilation=1, pt=1, dist_type="l2", restricted_radius=False,
                 reflect_bounds=True, full_ws=True, topk_mode="all", self_action=None, use_adj=False,
                 normalize_bwd=False, k_agg=-1, off_Hq=0, off_Wq=0, itype="float", shard=None):
-        check_common(pt, topk_mode, self_action, normalize_bwd, dist_type, itype)
+        each = topk_mode == "each"  # top-k inside every group of wr*wr candidates (impl/refinement.py:99-106)
+        if self_action == "anchor_each":  # impl/refinement.py:76-84: any "anchor*" anchors every group
+            self_action = "anchor"
+        check_common(pt, "all" if each else topk_mode, self_action, normalize_bwd, dist_type, itype)
+        if each and shard is not None:
+            raise NotImplementedError("stnls_b200: frame shards support topk_mode='all' only")
         assert isinstance(ps, int) and (ps > 0), f"patch size is invalid [{ps}]"
         q_cl = ops.pack_cl(vid0, nheads)
         k_cl = ops.pack_cl(vid1, nheads)
@@ -67,13 +72,20 @@ class RefineSearchFunction(th.autograd.Function):
             k_reflect, k_full = bool(reflect_bounds), bool(full_ws)
         flows_k = flows_k.contiguous()
         L = Ks * wr * wr
-        fused = (k <= 0) or (min(k, L) - (1 if anchor else 0) <= ops.MAX_FUSED_K)
+        fused = not each and ((k <= 0) or (min(k, L) - (1 if anchor else 0) <= ops.MAX_FUSED_K))
         geom = ops.make_geom(B, HD, T, F, qH, qW, kH, kW, stride0, tq0, Tq, tk0, Tk)
         opts = SearchOpts(ws, wt, Ks, wr, ps, k if fused else -1, stride0, strideQ_k, dilation, stride1_k,
                           int(k_reflect), int(k_full), 0 if use_adj else -(ps // 2), off_Hq, off_Wq,
                           dist_type_i, int(itype == "int"), int(anchor), flows_k.shape[1], 0)
         dists, inds, kselect, reflect = ops.search_forward(q_cl, k_cl, flows_k, geom, opts)
-        if not fused:
+        if each:
+            lead = dists.shape[:-1]
+            dists, inds = topk_each(dists.view(lead + (Ks, wr * wr)), inds.view(lead + (Ks, wr * wr, 3)), k,
+                                    descending, anchor_self=anchor)
+            if kselect is not None:  # every entry of a group carries the group index
+                kselect = kselect.view(lead + (Ks, wr * wr))[..., :dists.shape[-1]].reshape(lead + (-1,)).contiguous()
+            dists, inds = dists.reshape(lead + (-1,)).contiguous(), inds.reshape(lead + (-1, 3)).contiguous()
+        elif not fused:
             dists, inds, kselect = topk_fallback(dists, inds, k, anchor, descending, kselect)
 
         # the backward honours the *module's* reflect_bounds (impl/refinement.py:147-167)

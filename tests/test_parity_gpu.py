@@ -172,6 +172,11 @@ REFINE_CASES = [
     dict(name="refine_keepall", itype="float", wr=2, k=-1, Ks=3, self_action="anchor", dist_type="l2", stride0=1,
          stride1=1.0),
     dict(name="refine_manyK", itype="int", wr=1, k=-1, Ks=40, self_action=None, dist_type="l2", stride0=2, stride1=1),
+    # topk_mode="each": top-k inside every group of wr*wr candidates (impl/refinement.py:99-106)
+    dict(name="refine_each_int", itype="int", wr=3, k=3, Ks=4, self_action=None, dist_type="l2", stride0=1, stride1=1,
+         topk_mode="each"),
+    dict(name="refine_each_float_anchor", itype="float", wr=3, k=2, Ks=5, self_action="anchor_each", dist_type="prod",
+         stride0=2, stride1=0.5, topk_mode="each"),
 ]
 
 
@@ -193,7 +198,7 @@ def refine_inputs(c, oracle):
 def test_refine_forward(c, cuda, oracle):
     q, k, v, fl, HD = refine_inputs(c, oracle)
     kw = dict(nheads=HD, stride0=c["stride0"], stride1=c["stride1"], dist_type=c["dist_type"],
-              self_action=c["self_action"], itype=c["itype"])
+              self_action=c["self_action"], itype=c["itype"], topk_mode=c.get("topk_mode", "all"))
     d_ref, i_ref, ks_ref, rf_ref = oracle.refine_forward(q, k, fl, 3, 1, c["wr"], c["k"], -1, 3, **kw)
     search = stnls_b200.search.RefineSearch(3, 1, c["wr"], c["k"], -1, 3, **kw)
     d, i = search(q.to(cuda), k.to(cuda), fl.to(cuda))
@@ -205,7 +210,7 @@ def test_refine_forward(c, cuda, oracle):
 def test_refine_backward(c, cuda, oracle):
     q, k, v, fl, HD = refine_inputs(c, oracle)
     kw = dict(nheads=HD, stride0=c["stride0"], stride1=c["stride1"], dist_type=c["dist_type"],
-              self_action=c["self_action"], itype=c["itype"])
+              self_action=c["self_action"], itype=c["itype"], topk_mode=c.get("topk_mode", "all"))
     flt = c["itype"] == "float"
     # oracle forward provides kselect / reflect for the oracle backward
     d_ref, i_ref, ks_ref, rf_ref = oracle.refine_forward(q, k, fl, 3, 1, c["wr"], c["k"], -1, 3, **kw)
@@ -407,3 +412,32 @@ def test_fwd_anchor_properties(stride1, dist_type, cuda):
         got = firsts[2][1][:, 0, :, :, :, si]
         assert th.allclose(got[..., 1], fh - grid_h, 1e-3, 1e-3)
         assert th.allclose(got[..., 2], fw - grid_w, 1e-3, 1e-3)
+
+
+@pytest.mark.parametrize("itype", ["int", "float"])
+@pytest.mark.parametrize("dist_type", ["l2", "prod"])
+def test_refine_anchor_each_reproduces_search(itype, dist_type, cuda):
+    """tests/search/test_refinement.py:225-305 (test_anchor_fwd) on the CUDA path: refining the per-frame top-k of
+    a search with k=1, topk_mode="each", self_action="anchor_each" gives the search's own results back, with and
+    without window re-centring."""
+    ws, wt, wr, ps, stride0, HD = 3, 1, 1, 3, 1, 2
+    stride1 = 1 if itype == "int" else 0.5
+    B, T, F, H, W = 1, 5, 8, 32, 32
+    W_t = 2 * wt + 1
+    gen = th.Generator().manual_seed(321)
+    vid0 = (th.rand((B, T, F, H, W), generator=gen) - 0.5).to(cuda)
+    vid1 = (th.rand((B, T, F, H, W), generator=gen) - 0.5).to(cuda)
+    flows = (2 * th.rand((B, T, W_t - 1, 2, H, W), generator=gen)).to(cuda)
+    k0 = 5
+    search0 = stnls_b200.search.NonLocalSearch(ws, wt, ps, k0, HD, stride0=stride0, stride1=stride1, full_ws=True,
+                                               self_action=None, dist_type=dist_type, topk_mode="each", itype=itype)
+    d0, i0 = search0(vid0, vid1, flows)
+    assert d0.shape[-1] == W_t * k0
+    for full_ws in (False, True):
+        refine = stnls_b200.search.RefineSearch(ws, wt, wr, 1, -1, ps, HD, stride0=stride0, stride1=stride1,
+                                                full_ws=full_ws, self_action="anchor_each", dist_type=dist_type,
+                                                topk_mode="each", itype=itype)
+        dr, ir = refine(vid0, vid1, i0)
+        assert dr.shape == d0.shape
+        assert th.allclose(d0, dr, 1e-2, 1e-3, equal_nan=True)
+        assert th.allclose(i0.float(), ir.float(), 1e-3, 1e-3, equal_nan=True)
