@@ -339,6 +339,22 @@ def refine_forward(vid0, vid1, flows, ws, wt, wr, k, kr, ps, nheads=1, stride0=4
     return dists, inds, kselect, (reflect.bool() if reflect is not None else None)
 
 
+def normz_bwd(grad_vid0, grad_vid1, ps, stride0, stride1):
+    """normalize_bwd=True: lib/stnls/search/shared.py:59-97 (fold of ones, cropped, divides the grads in place)"""
+    import torch.nn.functional as F
+    assert int(stride1) == stride1, "stride1 must be an int."
+    B, T, C, H, W = grad_vid0.shape
+    for g, stride in ((grad_vid0, int(stride0)), (grad_vid1, int(stride1))):
+        nH, nW = (H - 1) // stride + 1, (W - 1) // stride + 1
+        counts = th.ones((1, ps * ps, nH * nW))
+        pad = (ps - 1) // 2
+        Hp, Wp = H + 2 * pad, W + 2 * pad
+        sH, sW = (Hp - H + 1) // 2, (Wp - W + 1) // 2
+        counts = F.fold(counts, (Hp, Wp), [ps] * 2, 1, [0, 0], stride)
+        g /= counts[..., sH:sH + H, sW:sW + W]
+    return grad_vid0, grad_vid1
+
+
 # ---------------------------------------------------------------------------------------------
 #   WeightedPatchSum == NonLocalGatherAdd
 # ---------------------------------------------------------------------------------------------

@@ -12,7 +12,7 @@ Differences that are visible to a caller (all documented in DESIGN.md):
     "anchor_and_remove_ref_frame", topk_mode "each" / "none" -- run the forward kernel in keep-all mode and
     then follow impl/non_local_search.py:88-139 step by step (per-frame anchoring is the kernel in
     csrc/anchor.cu, the selections are stable torch sorts, as in lib/stnls/nn/topk.py);
-  * pt != 1, normalize_bwd=True and ws_interior != ws raise NotImplementedError.
+  * pt != 1 and ws_interior != ws raise NotImplementedError.
 """
 import torch as th
 
@@ -110,12 +110,29 @@ def check_common(pt, topk_mode, self_action, normalize_bwd, dist_type, itype, nl
         raise NotImplementedError("stnls_b200: only topk_mode='all' is implemented")
     elif self_action not in FUSED_ACTIONS:
         raise NotImplementedError(f"stnls_b200: self_action [{self_action}] is not implemented")
-    if normalize_bwd:
-        raise NotImplementedError("stnls_b200: normalize_bwd=True is not implemented")
     if dist_type not in DIST_MENU:
         raise KeyError(dist_type)
     if itype not in ("int", "float"):
         raise ValueError(f"Uknown itype [{itype}]")
+
+
+def normz_bwd(grad_vid0, grad_vid1, ps, stride0, stride1):
+    """normalize_bwd=True (lib/stnls/search/shared.py:59-97): the video gradients are divided by the number of
+    ps x ps patches, on stride-`stride0` (grad_vid0) / stride-`stride1` (grad_vid1) grids, that cover each pixel --
+    the reference folds a tensor of ones; the counts are separable, so two device vectors from
+    stnls_overlap_counts do the same."""
+    assert int(stride1) == stride1, "stride1 must be an int."
+    assert grad_vid0.dim() == 5, "normalize_bwd expects (B,T,C,H,W) videos (shared.py:68)"
+    H, W = grad_vid0.shape[-2:]
+    pad = (ps - 1) // 2
+    for g, stride in ((grad_vid0, int(stride0)), (grad_vid1, int(stride1))):
+        nH, nW = (H - 1) // stride + 1, (W - 1) // stride + 1
+        # F.fold's own shape check: the ones tensor has nH*nW blocks, the padded plane (H+2*pad) must hold exactly that
+        if (H + 2 * pad - ps) // stride + 1 != nH or (W + 2 * pad - ps) // stride + 1 != nW:
+            raise RuntimeError("normalize_bwd: fold block count does not match (ps must be odd)")
+        ch, _ = ops.overlap_counts(H, nH, ps, stride, 1, -pad, g.device)
+        cw, _ = ops.overlap_counts(W, nW, ps, stride, 1, -pad, g.device)
+        g /= (ch.float()[:, None] * cw.float()[None, :])
 
 
 def shard_of(shard, T):
@@ -189,6 +206,7 @@ class NonLocalSearchFunction(th.autograd.Function):
         ctx.geom, ctx.opts = geom, opts
         ctx.vid_shapes = (tuple(vid0.shape), tuple(vid1.shape))
         ctx.nheads, ctx.k_agg, ctx.itype, ctx.flow_ndim = nheads, k_agg, itype, flow_ndim
+        ctx.normz = (ps, stride0, stride1) if normalize_bwd else None
         return dists, inds
 
     @staticmethod
@@ -206,6 +224,8 @@ class NonLocalSearchFunction(th.autograd.Function):
                                              ctx.geom, ctx.opts, flows_grad)
         g0 = ops.unpack_cl(gq, ctx.vid_shapes[0], ctx.nheads)
         g1 = ops.unpack_cl(gk, ctx.vid_shapes[1], ctx.nheads)
+        if ctx.normz is not None:
+            normz_bwd(g0, g1, *ctx.normz)
         if gflows is not None and ctx.flow_ndim == 6:
             gflows = gflows[:, 0].contiguous()
         return (g0, g1, gflows) + (None,) * 23

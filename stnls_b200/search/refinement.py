@@ -9,7 +9,7 @@ import torch as th
 from .. import ops
 from .._C import SearchOpts
 from ..utils import extract_pairs
-from .non_local_search import DIST_MENU, check_common, shard_of, topk_each, topk_fallback
+from .non_local_search import DIST_MENU, check_common, normz_bwd, shard_of, topk_each, topk_fallback
 
 
 def filter_k(inds, kr):
@@ -99,6 +99,7 @@ class RefineSearchFunction(th.autograd.Function):
         ctx.nheads, ctx.k_agg, ctx.itype = nheads, k_agg, itype
         ctx.flows_shape = tuple(flows_k.shape)
         ctx.flows_in_shape, ctx.Ks_in = flows_in_shape, Ks_in
+        ctx.normz = (ps, stride0, stride1) if normalize_bwd else None  # impl/refinement.py:175-176
         return dists, inds
 
     @staticmethod
@@ -121,6 +122,8 @@ class RefineSearchFunction(th.autograd.Function):
                                              reflect, ctx.geom, ctx.opts, flows_grad)
         g0 = ops.unpack_cl(gq, ctx.vid_shapes[0], ctx.nheads)
         g1 = ops.unpack_cl(gk, ctx.vid_shapes[1], ctx.nheads)
+        if ctx.normz is not None:
+            normz_bwd(g0, g1, *ctx.normz)
         if gflows is not None:
             Ks = gflows.shape[-2]
             if Ks != ctx.Ks_in:  # offsets dropped by `kr` get zero gradient

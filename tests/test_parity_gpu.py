@@ -441,3 +441,24 @@ def test_refine_anchor_each_reproduces_search(itype, dist_type, cuda):
         assert dr.shape == d0.shape
         assert th.allclose(d0, dr, 1e-2, 1e-3, equal_nan=True)
         assert th.allclose(i0.float(), ir.float(), 1e-3, 1e-3, equal_nan=True)
+
+
+@pytest.mark.parametrize("stride0,stride1", [(1, 1), (2, 1), (2, 2)])
+def test_normalize_bwd(stride0, stride1, cuda, oracle):
+    """normalize_bwd=True divides the video gradients by the patch-overlap counts (lib/stnls/search/shared.py:59-97)."""
+    c = dict(name="normz", B=1, T=3, F=4, H=17, W=20, HD=2, ws=3, wt=1, ps=3, k=4, stride0=stride0, stride1=stride1,
+             dist_type="l2", self_action=None, itype="int", flow="int")
+    q, k, v, flows, kw = build_case(c)
+    grads = []
+    for normalize in (False, True):
+        search = stnls_b200.search.NonLocalSearch(c["ws"], c["wt"], c["ps"], c["k"], normalize_bwd=normalize, **kw)
+        qg, kg = q.to(cuda).requires_grad_(True), k.to(cuda).requires_grad_(True)
+        d, i = search(qg, kg, flows.to(cuda))
+        gd = th.randn(d.shape, generator=th.Generator().manual_seed(5))
+        gd = th.where(th.isfinite(d.detach().cpu()), gd, th.zeros_like(gd))
+        (d * gd.to(cuda)).sum().backward()
+        grads.append((qg.grad.cpu(), kg.grad.cpu()))
+    e0, e1 = oracle.normz_bwd(grads[0][0].clone(), grads[0][1].clone(), c["ps"], stride0, stride1)
+    assert_close(grads[1][0], e0, 1e-6, 1e-5, "normalize_bwd grad_q")
+    assert_close(grads[1][1], e1, 1e-6, 1e-5, "normalize_bwd grad_k")
+    assert not th.allclose(grads[1][0], grads[0][0])
