@@ -240,6 +240,14 @@ def run_product(args):
             dist.barrier()
         th.cuda.synchronize()
 
+    def agree(flag):
+        """True when `flag` holds on every rank (ranks must take the same path through the collectives below)"""
+        if world == 1:
+            return bool(flag)
+        t = th.tensor([1.0 if flag else 0.0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return float(t[0]) > 0.5
+
     # ---- value: inputs resident in HBM -------------------------------------------------------
     resident = [t.to(dev) for t in host]
     # the timed steps' inputs are cloned BEFORE the warm-up so that the warm-up steps grow the caching
@@ -285,6 +293,7 @@ def run_product(args):
     elif args.graph != "off" and world > 1 and model.halo_kind != "peer":
         graph_note = "graph replay at N>1 is only used with the peer-memory halo exchange; eager timing reported"
     elif args.graph != "off":
+        cg = None
         try:
             static = [t.detach().clone() for t in resident]
             leafs = static[:3] + ([static[3]] if flt else [])
@@ -309,12 +318,19 @@ def run_product(args):
                 for _ in range(2):
                     captured()
             cur.wait_stream(cap)
-            barrier()
+            th.cuda.synchronize()
             l0 = ops.LAUNCHES
             cg = th.cuda.CUDAGraph()
             with th.cuda.graph(cg):
                 graph_out = captured()
             per_graph = ops.LAUNCHES - l0
+        except Exception as exc:  # capture not possible here: the eager number stands
+            graph_note = f"graph capture failed: {type(exc).__name__}: {exc}"[:200]
+            cg = None
+            th.cuda.synchronize()
+        if not agree(cg is not None):   # every rank replays, or none does
+            cg = None
+        if cg is not None:
             for _ in range(-(-args.warmup // unit)):
                 cg.replay()
             barrier()
@@ -334,10 +350,6 @@ def run_product(args):
                 print(f"[rank {rank}] graph per-step ms:", [round(a.elapsed_time(b), 3) for a, b in gevs], file=sys.stderr, flush=True)
             clk = gclk
             del cg, graph_out, static
-        except Exception as exc:  # capture not possible here: the eager number stands
-            graph_note = f"graph capture failed: {type(exc).__name__}: {exc}"[:200]
-            graph_ms = None
-            th.cuda.synchronize()
 
     # ---- e2e: pinned host buffers in, results back to pinned host buffers ----------------------
     # Every step uploads its own q,k,v,flows,grad_out from pinned host memory and downloads out and the four
@@ -403,7 +415,7 @@ def run_product(args):
             lat_s += time.perf_counter() - t0
     d2h = sum(t.numel() * t.element_size() for t in pinned.values())
 
-    # pipelined form
+    # pipelined form, eager front end
     def pipelined(n):
         nxt = upload()
         for i in range(n):
@@ -417,22 +429,82 @@ def run_product(args):
     barrier()
     t0 = time.perf_counter()
     pipelined(args.steps)
-    e2e_s = time.perf_counter() - t0
+    e2e_eager_s = time.perf_counter() - t0
     assert all(bool(th.isfinite(t).all()) for t in pinned.values())
+    e2e_s, e2e_from = e2e_eager_s, "eager"
 
-    tt = th.tensor([t_ms, e2e_s * 1e3, graph_ms if graph_ms is not None else -1.0, lat_s * 1e3], dtype=th.float64, device=dev)
+    # pipelined form through stnls_b200.parallel.GraphedStep: two buffer slots, each with its own CUDA graph of the
+    # step; slot s is filled from pinned host memory on the copy-in stream while the other slot runs, results leave on
+    # the copy-out stream.  Per step the host enqueues the copies and one graph launch.
+    if graph_ms is not None and args.steps % 2 == 0:
+        gs = None
+        try:
+            from stnls_b200.parallel import GraphedStep
+            gs = GraphedStep(model, resident, slots=2, flows_grad=flt)
+        except Exception as exc:
+            graph_note = f"e2e graph path failed: {type(exc).__name__}: {exc}"[:200]
+            gs = None
+            th.cuda.synchronize()
+        if not agree(gs is not None):
+            gs = None
+        if gs is not None:
+            names = ["out", "grad_q", "grad_k", "grad_v"] + (["grad_flows"] if flt else [])
+            gpin = {n: th.empty(t.shape, dtype=t.dtype).pin_memory() for n, t in zip(names, gs.outputs[0])}
+            computed = [th.cuda.Event() for _ in range(2)]
+            drained = [th.cuda.Event() for _ in range(2)]
+            filled = [th.cuda.Event() for _ in range(2)]
+
+            def graphed(n):
+                for ev in computed + drained:
+                    ev.record(main)
+                for i in range(n):
+                    s = i % 2
+                    up.wait_event(computed[s])       # slot s' previous step has read its inputs
+                    with th.cuda.stream(up):
+                        for j in (0, 1, 3, 2, 4):
+                            gs.inputs[s][j].copy_(host[j], non_blocking=True)
+                        filled[s].record(up)
+                    main.wait_event(filled[s])
+                    main.wait_event(drained[s])      # slot s' previous results have left the device
+                    gs.replay(s)
+                    computed[s].record(main)
+                    down.wait_event(computed[s])
+                    with th.cuda.stream(down):
+                        for nme, t in zip(names, gs.outputs[s]):
+                            gpin[nme].copy_(t, non_blocking=True)
+                        drained[s].record(down)
+                th.cuda.synchronize()
+
+            graphed(2 * -(-args.warmup // 2))
+            barrier()
+            t0 = time.perf_counter()
+            graphed(args.steps)
+            e2e_graph_s = time.perf_counter() - t0
+            # same inputs every step: the graphed results must be the eager ones (atomics: tolerance)
+            same = all(bool(th.isfinite(gpin[n]).all()) and
+                       float((gpin[n] - pinned[n]).abs().max()) <= 1e-3 * max(1.0, float(pinned[n].abs().max()))
+                       for n in names)
+            if not same:
+                graph_note = "e2e graph path: results differ from the eager path; eager e2e reported"
+            # long steps gain nothing from the graph and lose the overlap inside the step: keep the faster driver
+            if agree(same) and agree(e2e_graph_s < e2e_eager_s):
+                e2e_s, e2e_from = e2e_graph_s, "graph"
+            del gs
+
+    tt = th.tensor([t_ms, e2e_s * 1e3, graph_ms if graph_ms is not None else -1.0, lat_s * 1e3, e2e_eager_s * 1e3],
+                   dtype=th.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ok = th.tensor([1.0 if graph_ms is not None else 0.0], device=dev)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if float(ok[0]) == 0.0:
             graph_ms = None
-    t_ms, e2e_ms, lat_ms = float(tt[0]), float(tt[1]), float(tt[3])
+    t_ms, e2e_ms, lat_ms, e2e_eager_ms = float(tt[0]), float(tt[1]), float(tt[3]), float(tt[4])
     if graph_ms is not None:
         graph_ms = float(tt[2])
     return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
                 launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h, graph_ms=graph_ms, graph_note=graph_note,
-                per_graph=per_graph, unit=unit, lat_ms=lat_ms)
+                per_graph=per_graph, unit=unit, lat_ms=lat_ms, e2e_from=e2e_from, e2e_eager_ms=e2e_eager_ms)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -591,11 +663,15 @@ def main():
             "e2e": {"value": e2e_val, "unit": "Gcandidates/s", "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"], "ms_per_step": e2e_ms,
                     "latency_ms_per_step": r["lat_ms"] / steps,
-                    "what": "every step: pinned host q,k,v,flows,grad_out -> device, fwd+bwd through the Python front end "
-                            "(eager, no graph), out + grads of q,k,v,flows -> pinned host.  value: the K steps pipelined "
-                            "(step i+1's uploads enqueued on a copy stream before step i's kernels, downloads on a second "
-                            "copy stream, one synchronize after the K steps; wall clock).  latency_ms_per_step: the same "
-                            "step with a barrier + synchronize on both sides of every step"},
+                    "through": "stnls_b200.parallel.GraphedStep (two buffer slots, one CUDA graph of the step each)"
+                               if r["e2e_from"] == "graph" else "eager Python front end",
+                    "eager_ms_per_step": r["e2e_eager_ms"] / steps,
+                    "what": "every step: pinned host q,k,v,flows,grad_out -> device, search -> softmax -> aggregation fwd+bwd, "
+                            "out + grads of q,k,v,flows -> pinned host; wall clock, one synchronize after the K steps.  "
+                            "value / ms_per_step: the K steps pipelined -- the next step's uploads run on a copy-in stream "
+                            "while the current step computes, results leave on a copy-out stream.  eager_ms_per_step: the "
+                            "same pipeline driven through the eager modules (host-bound when many ranks share the host).  "
+                            "latency_ms_per_step: eager, with a barrier + synchronize on both sides of every step"},
             "gpu_launches": r["per_graph"] * (steps // r["unit"]) if graphed else r["launches"],
             "timing": {"value_from": "cuda graph replay of the step (one launch per step; CUDA events around each replay)"
                                      if graphed else "eager enqueue through the Python front end",

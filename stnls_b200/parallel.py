@@ -274,3 +274,64 @@ class ShardedSearchAgg(th.nn.Module):
         v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
         out = self.agg(v_ext, weights, inds, shard=self.plan.shard)
         return out, dists, inds
+
+
+class GraphedStep:
+    """Forward + backward of a search/aggregation module captured in CUDA graphs over static buffers.
+
+    The eager front end needs about a millisecond of host time to enqueue one README-sized step (14 kernel
+    launches plus the autograd bookkeeping around them); a graph replay is one launch.  `slots` independent
+    buffer sets, each with its own graph, let a caller fill slot i+1 (host -> device copies on a copy stream)
+    while slot i runs.  With the peer-memory halo exchange the slots must be replayed round-robin in capture
+    order (each capture takes the next buffer of the exchange's double buffering) and `slots` must be even.
+
+        step = GraphedStep(model, (q, k, v, flows, grad_out), slots=2)
+        step.inputs[s][j].copy_(host_tensor, non_blocking=True)   # j: q, k, v, flows, grad_out
+        step.replay(s)                                            # on the current stream
+        step.outputs[s]                                           # (out, grad_q, grad_k, grad_v[, grad_flows])
+
+    model(q, k, v, flows) -> (out, dists, inds), e.g. ShardedSearchAgg.  The gradients are those of
+    sum(out * grad_out).  Shapes are frozen at construction.
+    """
+
+    def __init__(self, model, example, slots=2, flows_grad=True, warmup=2):
+        assert all(t.is_cuda for t in example), "GraphedStep needs CUDA tensors (no CPU fallback)"
+        peer = getattr(model, "peer", None)
+        if peer is not None and slots % 2:
+            raise ValueError("GraphedStep: the peer halo exchange is double-buffered, slots must be even")
+        if getattr(model, "halo_kind", "none") == "nccl":
+            raise NotImplementedError("GraphedStep: use the peer-memory halo exchange (halo='peer') at world size > 1")
+        self.model, self.slots = model, slots
+        self.inputs, self.outputs, self.graphs = [], [], []
+        self.dists, self.inds = [], []
+        cur, cap = th.cuda.current_stream(), th.cuda.Stream()
+        for s in range(slots):
+            bufs = [t.detach().clone() for t in example]
+            leafs = bufs[:3] + ([bufs[3]] if flows_grad and bufs[3].is_floating_point() else [])
+            for t in leafs:
+                t.requires_grad_(True)
+
+            def run(bufs=bufs, leafs=leafs):
+                out, dists, inds = model(bufs[0], bufs[1], bufs[2], bufs[3])
+                grads = th.autograd.grad(out, leafs, grad_outputs=bufs[4])
+                return (out.detach(),) + tuple(grads), dists.detach(), inds
+
+            if s == 0:  # warm-up off the capture: allocator, lazily built tables, symmetric-memory rendezvous
+                cap.wait_stream(cur)
+                with th.cuda.stream(cap):
+                    for _ in range(2 * warmup):  # an even count keeps the halo double buffering in step
+                        run()
+                cur.wait_stream(cap)
+                th.cuda.synchronize()
+            g = th.cuda.CUDAGraph()
+            with th.cuda.graph(g):
+                res, dists, inds = run()
+            self.inputs.append([t.detach() for t in bufs])  # aliases a caller may copy_ into (the leaves require grad)
+            self.outputs.append(res)
+            self.dists.append(dists)
+            self.inds.append(inds)
+            self.graphs.append(g)
+
+    def replay(self, slot):
+        self.graphs[slot].replay()
+        return self.outputs[slot]
