@@ -639,7 +639,7 @@ def main():
                 "frac": achieved / peak,
                 "traffic": load_traffic(args.workload, dom) if world == 1 else None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg[dom]["bytes"], "ms_per_launch": kt[dom]["ms_per_launch"],
-                "share_of_step": kt[dom]["ms_per_step"] / eager_ms}
+                "share_of_step": kt[dom]["ms_per_step"] / ms_per_step}
     clocks = r["clocks"]
     mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965
     fma_peak = 148 * 128 * 2 * mhz * 1e6 / 1e12
