@@ -253,7 +253,8 @@ def run_product(args):
     # the timed steps' inputs are cloned BEFORE the warm-up so that the warm-up steps grow the caching
     # allocator to its steady-state size (otherwise the first timed step pays for cudaMalloc)
     fresh = [[t.detach().clone() for t in resident] for _ in range(args.steps)]
-    for _ in range(args.warmup):
+    # NCCL sets its send/recv channels up lazily, over several calls: settle them before the warm-up proper
+    for _ in range(args.warmup + (8 if model.halo_kind == "nccl" else 0)):
         step(*[t.detach().clone() for t in resident])
     barrier()
     evs = []
@@ -288,9 +289,7 @@ def run_product(args):
     # N>1: the peer-memory halo exchange alternates between two buffers per tag, so a graph holds TWO steps (the
     # buffer parity is back where it started after each replay), with the L2 flush between them inside the graph.
     unit = 1 if world == 1 else 2
-    if args.graph != "off" and args.steps % unit:
-        graph_note = "graph replay needs an even --steps at N>1; eager timing reported"
-    elif args.graph != "off" and world > 1 and model.halo_kind != "peer":
+    if args.graph != "off" and world > 1 and model.halo_kind != "peer":
         graph_note = "graph replay at N>1 is only used with the peer-memory halo exchange; eager timing reported"
     elif args.graph != "off":
         cg = None
@@ -305,9 +304,9 @@ def run_product(args):
                 loss = (out * static[4]).sum()
                 return out, th.autograd.grad(loss, leafs)
 
-            def captured():
+            def captured(nsteps=unit):
                 res = fwd_bwd()
-                for _ in range(unit - 1):
+                for _ in range(nsteps - 1):
                     flush.zero_()
                     res = fwd_bwd()
                 return res
@@ -323,7 +322,12 @@ def run_product(args):
             cg = th.cuda.CUDAGraph()
             with th.cuda.graph(cg):
                 graph_out = captured()
-            per_graph = ops.LAUNCHES - l0
+            per_graph = (ops.LAUNCHES - l0) // unit
+            cg_tail = None
+            if args.steps % unit:  # odd --steps at N>1: one single-step graph, replayed once after the two-step ones
+                cg_tail = th.cuda.CUDAGraph()
+                with th.cuda.graph(cg_tail):
+                    tail_out = captured(1)
         except Exception as exc:  # capture not possible here: the eager number stands
             graph_note = f"graph capture failed: {type(exc).__name__}: {exc}"[:200]
             cg = None
@@ -336,11 +340,11 @@ def run_product(args):
             barrier()
             gevs = []
             with ClockSampler(local) as gclk:
-                for i in range(args.steps // unit):
+                for gr in [cg] * (args.steps // unit) + ([cg_tail] if args.steps % unit else []):
                     flush.zero_()
                     e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
                     e0.record()
-                    cg.replay()
+                    gr.replay()
                     e1.record()
                     gevs.append((e0, e1))
                 barrier()
@@ -349,7 +353,7 @@ def run_product(args):
             if os.environ.get("BENCH_DEBUG"):
                 print(f"[rank {rank}] graph per-step ms:", [round(a.elapsed_time(b), 3) for a, b in gevs], file=sys.stderr, flush=True)
             clk = gclk
-            del cg, graph_out, static
+            del cg, cg_tail, graph_out, static
 
     # ---- e2e: pinned host buffers in, results back to pinned host buffers ----------------------
     # Every step uploads its own q,k,v,flows,grad_out from pinned host memory and downloads out and the four
@@ -436,7 +440,7 @@ def run_product(args):
     # pipelined form through stnls_b200.parallel.GraphedStep: two buffer slots, each with its own CUDA graph of the
     # step; slot s is filled from pinned host memory on the copy-in stream while the other slot runs, results leave on
     # the copy-out stream.  Per step the host enqueues the copies and one graph launch.
-    if graph_ms is not None and args.steps % 2 == 0:
+    if graph_ms is not None:
         gs = None
         try:
             from stnls_b200.parallel import GraphedStep
@@ -672,10 +676,10 @@ def main():
                             "while the current step computes, results leave on a copy-out stream.  eager_ms_per_step: the "
                             "same pipeline driven through the eager modules (host-bound when many ranks share the host).  "
                             "latency_ms_per_step: eager, with a barrier + synchronize on both sides of every step"},
-            "gpu_launches": r["per_graph"] * (steps // r["unit"]) if graphed else r["launches"],
+            "gpu_launches": r["per_graph"] * steps if graphed else r["launches"],
             "timing": {"value_from": "cuda graph replay of the step (one launch per step; CUDA events around each replay)"
                                      if graphed else "eager enqueue through the Python front end",
-                       "ms_per_step_eager": eager_ms, "kernel_nodes_per_graph": r["per_graph"] if graphed else None,
+                       "ms_per_step_eager": eager_ms, "kernel_launches_per_step": r["per_graph"] if graphed else None,
                        "steps_per_graph": r["unit"] if graphed else None,
                        "note": r["graph_note"] or "`kernels` and `roofline` come from the eager pass (per-launch CUDA events)"},
             "clocks": clocks, "roofline": roofline,
@@ -687,6 +691,8 @@ def main():
         line["cpu_baseline"] = {"value": c / t / 1e9, "unit": "Gcandidates/s", "cores": cores, "kind": "port",
                                 "sample": f"{n} pass(es) of the same pipeline on a {crop}x{crop} crop (T={wl['T']}), "
                                           f"oracle/stnls_oracle.c with OpenMP, {t:.1f} s of CPU work"}
+    if graphed and r["unit"] > 1:
+        line["config"]["l2_policy"] += "; graph replays hold two steps with the same flush between them"
     print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist
