@@ -193,6 +193,21 @@ def load_traffic(workload, kernel):
         return None
 
 
+def bind_near_gpu(local):
+    """N>1: run this rank's host thread on the CPUs next to its GPU (NVML's ideal affinity), so that the pinned
+    host buffers of the e2e loop land on the GPU's NUMA node and 8 ranks do not push all copies through one socket.
+    Returns the number of CPUs bound to, or None when NVML is not usable (nothing changes then)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(th.cuda.get_device_properties(local).uuid)
+        h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid if not uuid.startswith("GPU-") else uuid).encode())
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def run_product(args):
     import torch.distributed as dist
     import stnls_b200
@@ -205,7 +220,9 @@ def run_product(args):
         raise SystemExit("bench.py: no CUDA device (the product arm has no CPU path)")
     th.cuda.set_device(local)
     dev = th.device("cuda", local)
+    numa = None
     if world > 1:
+        numa = bind_near_gpu(local)   # before the pinned buffers are allocated (first touch decides their NUMA node)
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch N>1 with torchrun)"
 
@@ -508,7 +525,7 @@ def run_product(args):
         graph_ms = float(tt[2])
     return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
                 launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h, graph_ms=graph_ms, graph_note=graph_note,
-                per_graph=per_graph, unit=unit, lat_ms=lat_ms, e2e_from=e2e_from, e2e_eager_ms=e2e_eager_ms)
+                per_graph=per_graph, unit=unit, lat_ms=lat_ms, e2e_from=e2e_from, e2e_eager_ms=e2e_eager_ms, numa=numa)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -691,6 +708,9 @@ def main():
         line["cpu_baseline"] = {"value": c / t / 1e9, "unit": "Gcandidates/s", "cores": cores, "kind": "port",
                                 "sample": f"{n} pass(es) of the same pipeline on a {crop}x{crop} crop (T={wl['T']}), "
                                           f"oracle/stnls_oracle.c with OpenMP, {t:.1f} s of CPU work"}
+    if world > 1:
+        line["config"]["host_affinity"] = (f"rank threads bound to the {r['numa']} CPUs NVML lists for their GPU" if r["numa"]
+                                           else "not bound (NVML affinity unavailable)")
     if graphed and r["unit"] > 1:
         line["config"]["l2_policy"] += "; graph replays hold two steps with the same flush between them"
     print(json.dumps(line), flush=True)
