@@ -303,13 +303,13 @@ def run_product(args):
     # waits for Python.  A graph replay is one launch per step, so `value` is what the kernels deliver.  The
     # eager pass stays: its per-launch CUDA events feed the kernel table / roofline.
     graph_ms, graph_note, per_graph = None, None, 0
-    # N>1: the peer-memory halo exchange alternates between two buffers per tag, so a graph holds TWO steps (the
-    # buffer parity is back where it started after each replay), with the L2 flush between them inside the graph.
+    # N>1: the peer-memory halo exchange alternates between two buffers per tag, so the step is captured twice (one
+    # graph per buffer parity) and the two graphs are replayed in turn, as GraphedStep does with its slots.
     unit = 1 if world == 1 else 2
     if args.graph != "off" and world > 1 and model.halo_kind != "peer":
         graph_note = "graph replay at N>1 is only used with the peer-memory halo exchange; eager timing reported"
     elif args.graph != "off":
-        cg = None
+        cgs = None
         try:
             static = [t.detach().clone() for t in resident]
             leafs = static[:3] + ([static[3]] if flt else [])
@@ -321,47 +321,38 @@ def run_product(args):
                 loss = (out * static[4]).sum()
                 return out, th.autograd.grad(loss, leafs)
 
-            def captured(nsteps=unit):
-                res = fwd_bwd()
-                for _ in range(nsteps - 1):
-                    flush.zero_()
-                    res = fwd_bwd()
-                return res
-
             cur, cap = th.cuda.current_stream(), th.cuda.Stream()
             cap.wait_stream(cur)
             with th.cuda.stream(cap):
-                for _ in range(2):
-                    captured()
+                for _ in range(2 * unit):
+                    fwd_bwd()
             cur.wait_stream(cap)
             th.cuda.synchronize()
             l0 = ops.LAUNCHES
-            cg = th.cuda.CUDAGraph()
-            with th.cuda.graph(cg):
-                graph_out = captured()
+            cgs, graph_out = [], None
+            for _ in range(unit):   # N>1: one graph per halo buffer parity, replayed in capture order
+                gph = th.cuda.CUDAGraph()
+                with th.cuda.graph(gph):
+                    graph_out = fwd_bwd()
+                cgs.append(gph)
             per_graph = (ops.LAUNCHES - l0) // unit
-            cg_tail = None
-            if args.steps % unit:  # odd --steps at N>1: one single-step graph, replayed once after the two-step ones
-                cg_tail = th.cuda.CUDAGraph()
-                with th.cuda.graph(cg_tail):
-                    tail_out = captured(1)
         except Exception as exc:  # capture not possible here: the eager number stands
             graph_note = f"graph capture failed: {type(exc).__name__}: {exc}"[:200]
-            cg = None
+            cgs = None
             th.cuda.synchronize()
-        if not agree(cg is not None):   # every rank replays, or none does
-            cg = None
-        if cg is not None:
-            for _ in range(-(-args.warmup // unit)):
-                cg.replay()
+        if not agree(cgs is not None):   # every rank replays, or none does
+            cgs = None
+        if cgs is not None:
+            for i in range(unit * -(-args.warmup // unit)):
+                cgs[i % unit].replay()
             barrier()
             gevs = []
             with ClockSampler(local) as gclk:
-                for gr in [cg] * (args.steps // unit) + ([cg_tail] if args.steps % unit else []):
+                for i in range(args.steps):
                     flush.zero_()
                     e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
                     e0.record()
-                    gr.replay()
+                    cgs[i % unit].replay()
                     e1.record()
                     gevs.append((e0, e1))
                 barrier()
@@ -370,7 +361,7 @@ def run_product(args):
             if os.environ.get("BENCH_DEBUG"):
                 print(f"[rank {rank}] graph per-step ms:", [round(a.elapsed_time(b), 3) for a, b in gevs], file=sys.stderr, flush=True)
             clk = gclk
-            del cg, cg_tail, graph_out, static
+            del cgs, graph_out, static
 
     # ---- e2e: pinned host buffers in, results back to pinned host buffers ----------------------
     # Every step uploads its own q,k,v,flows,grad_out from pinned host memory and downloads out and the four
@@ -697,7 +688,7 @@ def main():
             "timing": {"value_from": "cuda graph replay of the step (one launch per step; CUDA events around each replay)"
                                      if graphed else "eager enqueue through the Python front end",
                        "ms_per_step_eager": eager_ms, "kernel_launches_per_step": r["per_graph"] if graphed else None,
-                       "steps_per_graph": r["unit"] if graphed else None,
+                       "graphs": r["unit"] if graphed else None,
                        "note": r["graph_note"] or "`kernels` and `roofline` come from the eager pass (per-launch CUDA events)"},
             "clocks": clocks, "roofline": roofline,
             "roofline_fma": roofline_fma, "kernels": kt}
@@ -711,8 +702,6 @@ def main():
     if world > 1:
         line["config"]["host_affinity"] = (f"rank threads bound to the {r['numa']} CPUs NVML lists for their GPU" if r["numa"]
                                            else "not bound (NVML affinity unavailable)")
-    if graphed and r["unit"] > 1:
-        line["config"]["l2_policy"] += "; graph replays hold two steps with the same flush between them"
     print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist
