@@ -26,6 +26,19 @@ void stnls_set_error(const char* fmt, ...);
     }                                                                        \
   } while (0)
 
+// -------- index decode: x = q * d + rem, x >= 0.  The 64-bit division is a ~100-instruction software routine;
+// every launch this library makes has fewer than 2^32 work items, so the 32-bit path is the one that runs.
+__device__ __forceinline__ int64_t divmod(int64_t x, int d, int& rem) {
+  if (x <= 0xffffffffLL) {
+    const unsigned q = (unsigned)x / (unsigned)d;
+    rem = (int)((unsigned)x - q * (unsigned)d);
+    return (int64_t)q;
+  }
+  const int64_t q = x / d;
+  rem = (int)(x - q * d);
+  return q;
+}
+
 // -------- reflect-once bounds (shared_kernel.cu:49-60) ---------------------------------------
 __device__ __forceinline__ int bnd(int v, int lim) {
   if (v < 0) return -v;

@@ -47,15 +47,15 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
   const stnls_search_opts& o = P.o;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P.nthreads) return;
-  const int c4 = (int)(idx % P.nquad) * 4;
-  int64_t wq = idx / P.nquad;
+  int c4, nw, nh, tl, hd;
+  int64_t wq = divmod(idx, P.nquad, c4);
+  c4 *= 4;
   int k_lo = 0, k_hi = P.K;
-  if (KSPLIT) { k_lo = (int)(wq % P.K); k_hi = k_lo + 1; wq /= P.K; }
-  int64_t r = wq;
-  const int nw = (int)(r % g.nW); r /= g.nW;
-  const int nh = (int)(r % g.nH); r /= g.nH;
-  const int tl = (int)(r % g.Tq); r /= g.Tq;
-  const int n = (int)r, hd = n % g.HD, b = n / g.HD;
+  if (KSPLIT) { wq = divmod(wq, P.K, k_lo); k_hi = k_lo + 1; }
+  int64_t r = divmod(wq, g.nW, nw);
+  r = divmod(r, g.nH, nh);
+  r = divmod(r, g.Tq, tl);
+  const int n = (int)r, b = (int)divmod(r, g.HD, hd);
   const int t = tl + g.tq0;
   const int ah = (nh * o.stride0) % g.kH, aw = (nw * o.stride0) % g.kW;
   const int rh = (MODE == 0) ? (nh * o.strideQ) % g.qH : ah;

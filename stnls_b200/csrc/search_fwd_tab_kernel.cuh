@@ -113,13 +113,11 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
 
   // -- decode query (shared_kernel.cu:76-98) --
   QueryCtx c;
-  int64_t r = wq;
-  c.nw = (int)(r % g.nW); r /= g.nW;
-  c.nh = (int)(r % g.nH); r /= g.nH;
-  c.tl = (int)(r % g.Tq); r /= g.Tq;
+  int64_t r = divmod(wq, g.nW, c.nw);
+  r = divmod(r, g.nH, c.nh);
+  r = divmod(r, g.Tq, c.tl);
   c.n = (int)r;
-  c.hd = c.n % g.HD;
-  c.b = c.n / g.HD;
+  c.b = (int)divmod(r, g.HD, c.hd);
   c.t = c.tl + g.tq0;
   c.ah = (c.nh * o.stride0) % g.kH;
   c.aw = (c.nw * o.stride0) % g.kW;

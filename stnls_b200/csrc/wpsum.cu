@@ -283,14 +283,14 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
   const int H = g.kH, W = g.kW;
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P.nthreads) return;
-  const int c4 = (int)(idx % P.nquad) * 4;
-  int64_t wq = idx / P.nquad;
+  int c4, nw, nh, tl;
+  int64_t wq = divmod(idx, P.nquad, c4);
+  c4 *= 4;
   int k_lo = 0, k_hi = o.K;
-  if (KSPLIT) { k_lo = (int)(wq % o.K); k_hi = k_lo + 1; wq /= o.K; }
-  int64_t r = wq;
-  const int nw = (int)(r % g.nW); r /= g.nW;
-  const int nh = (int)(r % g.nH); r /= g.nH;
-  const int tl = (int)(r % g.Tq); r /= g.Tq;
+  if (KSPLIT) { wq = divmod(wq, o.K, k_lo); k_hi = k_lo + 1; }
+  int64_t r = divmod(wq, g.nW, nw);
+  r = divmod(r, g.nH, nh);
+  r = divmod(r, g.Tq, tl);
   const int n = (int)r;
   const int t = tl + g.tq0;
   const int rh = (nh * o.stride0) % H, rw = (nw * o.stride0) % W;
