@@ -3,7 +3,7 @@ from . import search_flow as _search_flow_mod  # noqa: F401
 from .search_flow import run as search_flow  # noqa: F401
 from .search_flow import search_flow_th  # noqa: F401
 from . import non_local_attn  # noqa: F401
-from .non_local_attn import NonLocalAttention  # noqa: F401
+from .non_local_attn import NonLocalAttention, NonLocalAttentionStack  # noqa: F401
 
 
 def anchor_self_time(dists, inds, flows, wt, stride0, qH, qW, kH, kW):

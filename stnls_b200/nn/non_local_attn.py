@@ -141,6 +141,27 @@ class NonLocalAttention(nn.Module):
         return x.view(B, T, -1, H, W)
 
 
+class NonLocalAttentionStack(NonLocalAttention):
+    """lib/stnls/nn/non_local_attn_stack.py:53-147: the same block without the output projection -- forward returns
+    what the aggregator returns (with agg_name="gather" / "nlstack": the K-stacked video (B,HD,K,T,F_head,H,W) of
+    NonLocalGather), so that a caller can fuse the K neighbours itself."""
+
+    def __init__(self, attn_cfg, search_cfg, normz_cfg, agg_cfg):
+        attn_cfg = dict(attn_cfg)
+        attn_cfg["use_attn_projection"] = False  # the stack block has no projection (non_local_attn_stack.py:107-117)
+        super().__init__(attn_cfg, search_cfg, normz_cfg, agg_cfg)
+
+    def forward(self, vid, flows=None, state=None):
+        B, T, C, H, W = vid.shape
+        if self.use_flow:
+            flows = rescale_flows(flows, H, W)
+        vid = self.norm_layer(vid)
+        q_vid, k_vid, v_vid = self.get_qkv(vid)
+        dists, inds = self.run_search(q_vid, k_vid, flows, state)
+        weights, inds = self.normz(dists, inds)
+        return self.agg(v_vid, weights, inds)
+
+
 def init(cfg):
     """Split one flat config into the four the block takes (lib/stnls/nn/non_local_attn.py + api usage)."""
     cfg = AttrDict(cfg)

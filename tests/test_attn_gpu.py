@@ -61,3 +61,30 @@ def test_menus(cuda):
     assert isinstance(stnls_b200.normz.init(dict(normz_scale=5.0)), stnls_b200.normz.SoftmaxNormalize)
     with pytest.raises(NotImplementedError):
         stnls_b200.search.init(dict(search_name="n3mm", ws=3, wt=0))
+
+
+def test_attention_stack_sums_to_attention(cuda):
+    """NonLocalAttentionStack (lib/stnls/nn/non_local_attn_stack.py) with the K-stacked aggregator: summing its
+    output over K gives what the projection-free NonLocalAttention block with the weighted patch sum returns
+    (the reference's own ground truth for gather vs gather_add, tests/agg/test_gather_add.py:106-128)."""
+    from stnls_b200.nn.non_local_attn import NonLocalAttentionStack, NonLocalAttention, extract_config
+    base = dict(nheads=2, embed_dim=4, search_name="nls", ws=3, wt=1, ps=3, k=5, stride0=1, stride1=1.0,
+                dist_type="l2", self_action="anchor", itype="float", normz_scale=10, k_agg=-1, strideIn=1,
+                strideOut=1, use_attn_projection=False)
+    blocks = []
+    for cls, agg_name in ((NonLocalAttentionStack, "gather"), (NonLocalAttention, "wpsum")):
+        cfg = AttrDict(dict(base, agg_name=agg_name))
+        th.manual_seed(9)
+        blocks.append(cls(extract_config(cfg, False), cfg, cfg, cfg).to(cuda))
+    g = th.Generator().manual_seed(10)
+    B, T, C, H, W = 1, 3, 8, 16, 16
+    vid = th.randn(B, T, C, H, W, generator=g).to(cuda)
+    flows = AttrDict(fflow=th.randn(B, T, 2, H, W, generator=g).to(cuda), bflow=th.randn(B, T, 2, H, W, generator=g).to(cuda))
+    vg = vid.clone().requires_grad_(True)
+    stack = blocks[0](vg, flows)
+    assert tuple(stack.shape) == (B, 2, 5, T, C // 2, H, W)
+    summed = blocks[1](vid, flows)                                  # (B,T,C,H,W)
+    got = stack.sum(2).permute(0, 2, 1, 3, 4, 5).reshape(B, T, C, H, W)
+    assert_close(got, summed, 1e-4, 1e-4, "stack.sum(K) vs weighted patch sum")
+    stack.square().mean().backward()
+    assert vg.grad is not None and bool(th.isfinite(vg.grad).all()) and float(vg.grad.abs().sum()) > 0
