@@ -19,3 +19,20 @@ def topk_each(dists, inds, k, descending, anchor_self=False):
     """stnls.nn.topk_each (lib/stnls/nn/topk.py:226-269), stable."""
     from ..search.non_local_search import topk_each as impl
     return impl(dists, inds, k, descending, anchor_self=anchor_self)
+
+
+def topk(dists, inds, k, dim=1, anchor=False, descending=True, unique=False, return_order=False):
+    """stnls.nn.topk (lib/stnls/nn/topk.py:65-95) for the layouts the searches produce: the candidate axis `dim` of
+    dists is moved last, selected with a stable sort (anchored: slot 0 stays), and moved back."""
+    if unique:
+        raise NotImplementedError("stnls_b200: unique top-k is outside the hot path")
+    if not (k > 0):
+        return (dists, inds, None) if return_order else (dists, inds)
+    from ..search.non_local_search import topk_fallback
+    import torch as th
+    d = dists.movedim(dim, -1)
+    i = inds.movedim(dim, -2)
+    pos = th.arange(d.shape[-1], device=d.device).expand(d.shape)
+    dk, ik, order = topk_fallback(d.contiguous(), i.contiguous(), k, anchor, descending, pos.contiguous())
+    dk, ik, order = dk.movedim(-1, dim), ik.movedim(-2, dim), order.movedim(-1, dim)
+    return (dk, ik, order) if return_order else (dk, ik)
