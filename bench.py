@@ -627,7 +627,17 @@ def main():
         run_reference(args)
         return
 
-    r = run_product(args)
+    # stdout carries the one JSON line only: whatever libraries print on fd 1 meanwhile (NCCL's version line at N>1)
+    # is sent to stderr, and fd 1 comes back for the final print
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        r = run_product(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
     if r["rank"] != 0:
         return
     wl, world, steps = r["wl"], r["world"], args.steps
