@@ -6,7 +6,7 @@ for w in c2 c3 c4s; do tail -1 $S/bench_$w.json > profiles/${TAG}_bench_$w.json;
 tail -1 $S/bench_ref_c2.json > profiles/${TAG}_bench_ref_c2.json
 tail -4 $S/pytest_gpu.log > profiles/${TAG}_pytest_gpu.txt
 python tools/ncu_summary.py profiles/${TAG}_ncu_full_c2.json $S/full_*.ncu-rep
-python tools/ncu_phases.py $S/full_search_fwd_c2.ncu-rep search_fwd_tab_kernel.cuh:54-80=lattice_value search_fwd_tab_kernel.cuh:258-292=lattice search_fwd_tab_kernel.cuh:293-470=candidates search_fwd_tab_kernel.cuh:210-257=axis_tables search_fwd_tab_kernel.cuh:165-209=anchor_pass search_fwd_tab_kernel.cuh:471-500=select search_fwd_tab_kernel.cuh:501-530=write search_fwd_tab_kernel.cuh:84-164=setup > profiles/${TAG}_search_fwd_phases.txt
+python tools/ncu_phases.py $S/full_search_fwd_c2.ncu-rep search_fwd_tab_kernel.cuh:54-82=lattice_value search_fwd_tab_kernel.cuh:84-164=setup search_fwd_tab_kernel.cuh:165-204=anchor_pass search_fwd_tab_kernel.cuh:205-268=axis_tables search_fwd_tab_kernel.cuh:269-302=lattice search_fwd_tab_kernel.cuh:303-575=candidates search_fwd_tab_kernel.cuh:576-607=select search_fwd_tab_kernel.cuh:608-660=write > profiles/${TAG}_search_fwd_phases.txt
 python tools/ncu_smem.py $S/full_search_fwd_c2.ncu-rep 12 > profiles/${TAG}_search_fwd_smem.txt
 python - <<PY
 import json
