@@ -47,6 +47,21 @@ def _worker(rank, world, halo, port, ret):
         td = 1 if n in ("grad_q", "grad_k", "grad_v") else 2
         b = b.narrow(td, plan.a, plan.b - plan.a)
         errs[n] = float((a - b).abs().max())
+    if halo == "peer":
+        # GraphedStep over the sharded module: two slots replayed in turn (one per halo buffer parity), three rounds
+        search = stnls_b200.search.NonLocalSearch(ws, wt, ps, K, nheads=HD, stride1=0.5, dist_type="l2",
+                                                  self_action="anchor", itype="float")
+        agg = stnls_b200.agg.WeightedPatchSum(ps=ps, stride0=1, itype="float")
+        model = parallel.ShardedSearchAgg(search, agg, plan, scale=10.0, halo="peer")
+        sl = slice(plan.a, plan.b)
+        ins = [x[:, sl].to(dev) for x in (q, k, v)] + [flows[:, :, sl].to(dev), gout[:, :, sl].to(dev)]
+        step = parallel.GraphedStep(model, ins, slots=2)
+        worst = 0.0
+        for i in range(6):
+            res = step.replay(i % 2)
+            for a, b in zip(res, [got[0]] + got[3:]):
+                worst = max(worst, float((a - b).abs().max()))
+        errs["graphed"] = worst
     ret[rank] = errs
     dist.barrier()
     dist.destroy_process_group()
