@@ -462,3 +462,29 @@ def test_normalize_bwd(stride0, stride1, cuda, oracle):
     assert_close(grads[1][0], e0, 1e-6, 1e-5, "normalize_bwd grad_q")
     assert_close(grads[1][1], e1, 1e-6, 1e-5, "normalize_bwd grad_k")
     assert not th.allclose(grads[1][0], grads[0][0])
+
+
+@pytest.mark.parametrize("dist_type", ["l2", "prod"])
+def test_fwd_float_vs_int(dist_type, cuda):
+    """tests/search/test_non_local_search_bilin2d.py:58-150 (test_fwd_vs_int) on the CUDA path: with integer stride1
+    and integer optical flow the bilinear search equals the integer search, called the way the reference test calls
+    it -- forward(q, k, fflow, bflow), flows accumulated by nn.search_flow inside the module."""
+    ws, wt, ps, k, HD, stride0, stride1 = 3, 1, 3, -1, 2, 1, 1
+    B, T, F, H, W = 1, 3, 1, 10, 10
+    gen = th.Generator().manual_seed(0)
+    vid = th.rand((B, T, HD * F, H, W), generator=gen).to(cuda)
+    fflow = th.clamp(10 * th.randn((B, T, 2, H, W), generator=gen), -10, 10).round().to(cuda)
+    bflow = th.clamp(10 * th.randn((B, T, 2, H, W), generator=gen), -10, 10).round().to(cuda)
+    out = {}
+    for itype in ("float", "int"):
+        search = stnls_b200.search.NonLocalSearch(ws, wt, ps, k, HD, dist_type=dist_type, stride0=stride0,
+                                                  stride1=stride1, reflect_bounds=True, full_ws=True,
+                                                  self_action=None, itype=itype)
+        out[itype] = search(vid, vid, fflow, bflow)
+    d_te, i_te = out["float"]
+    d_gt, i_gt = out["int"]
+    ok = d_gt.abs() < 1e30
+    assert bool((ok == (d_te.abs() < 1e30)).all())
+    diff = ((d_te - d_gt).abs() / (d_gt.abs() + 1e-5))[ok]
+    assert float(diff.mean()) < 5e-3 and float(diff.max()) < 1e-4 + 5e-3
+    assert bool(((i_te - i_gt.float()).abs()[ok] < 1e-3).all())
