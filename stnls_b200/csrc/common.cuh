@@ -10,6 +10,9 @@
 
 // -------- errors ---------------------------------------------------------------------------
 void stnls_set_error(const char* fmt, ...);
+// host: frame-shard fields of a geometry are consistent (0 <= tq0, tq0+Tq <= T, 0 <= tk0, tk0+Tk <= T); `wt` >= 0
+// additionally requires the resident key frames to cover the temporal windows of the owned query frames
+int stnls_check_geom(const stnls_geom* g, int wt, const char* who);
 #define STNLS_REQUIRE(cond, ...)            \
   do {                                      \
     if (!(cond)) {                          \
@@ -52,6 +55,13 @@ __device__ __forceinline__ float bnd(float v, int lim) {
 }
 __device__ __forceinline__ bool inb(int v, int lim) { return (v >= 0) && (v <= lim - 1); }
 __device__ __forceinline__ bool inb(float v, int lim) { return (v >= 0) && (v <= (float)(lim - 1)); }
+// frame t (global index) is one of the key/value frames this rank holds, [tk0, tk0+Tk).  Every kernel tests this
+// before it forms a frame pointer: a frame inside the clip but outside the resident halo counts as invalid
+// (skipped) instead of being read or written out of bounds.  Unsharded: tk0 = 0, Tk = T, i.e. inb(t, T).
+__device__ __forceinline__ bool resident(int t, const stnls_geom& g) { return (unsigned)(t - g.tk0) < (unsigned)g.Tk; }
+__device__ __forceinline__ bool resident(float t, const stnls_geom& g) {
+  return (t >= (float)g.tk0) && (t <= (float)(g.tk0 + g.Tk - 1));
+}
 
 // -------- temporal window (shared_kernel.cu:307-312) -----------------------------------------
 __device__ __forceinline__ int time_tmax(int ti, int T, int wt) {

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
       const int* ind = reinterpret_cast<const int*>(P.inds) + oi * 3;
       const int p0 = bnd(t + ind[0], g.T);
       const int ph = ah + ind[1], pw = aw + ind[2];
-      if (!inb(p0, g.T)) continue;
+      if (!resident(p0, g)) continue;
       const float* kf = kb + (int64_t)(p0 - g.tk0) * kfs;
       float* gkf = gkb + (int64_t)(p0 - g.tk0) * kfs;
 #pragma unroll
@@ -147,8 +147,8 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
         if (!(inb(z.pp0, g.T) && inb(z.pph, g.kH) && inb(z.ppw, g.kW))) return z;
       }
       const float p0 = bnd(z.pp0, g.T);
-      if (!inb(p0, g.T)) return z;
       z.pt0 = __float2int_rn(p0);
+      if (!inb(p0, g.T) || !resident(z.pt0, g)) return z;
       z.valid = true;
       return z;
     };
@@ -359,6 +359,7 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   STNLS_REQUIRE(gq_cl && gk_cl && q_cl && k_cl && grad_dists && inds && g && o, "search_backward: null argument");
   STNLS_REQUIRE(g->Fp % 4 == 0, "search_backward: Fp must be a multiple of 4");
   STNLS_REQUIRE(o->dist_type == 0 || o->dist_type == 1, "Uknown distance type. Must be 0 (product) or 1 (l2)");
+  if (int rc = stnls_check_geom(g, -1, "search_backward")) return rc;
   BwdParams P;
   P.gq = gq_cl; P.gk = gk_cl; P.gflows = grad_flows; P.q = q_cl; P.k = k_cl; P.flows = flows;
   P.gd = grad_dists; P.gi = grad_inds; P.inds = inds; P.kselect = kselect; P.reflect = reflect;

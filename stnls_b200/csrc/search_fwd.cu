@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(256) search_fwd_kernel(const __grid_constant__
       if (active && gp.ok) {
         C chh, cww;
         cand_center(P, gp, s, chh, cww);
-        bool valid = inb(gp.t, g.T) && inb(chh, g.kH) && inb(cww, g.kW);
+        bool valid = resident(gp.t, g) && inb(chh, g.kH) && inb(cww, g.kW);
         if (valid) d = patch_dist<DIST>(P, qf, kbase + (int64_t)(gp.t - g.tk0) * kfs, c, chh, cww);
       }
       // position after the anchor swap (an involution inside the group)
@@ -299,6 +299,7 @@ extern "C" int stnls_search_forward(const float* q_cl, const float* k_cl, const 
   STNLS_REQUIRE(o->dist_type == 0 || o->dist_type == 1, "Uknown distance type. Must be 0 (product) or 1 (l2)");
   STNLS_REQUIRE(o->ps > 0, "search_forward: patch size is invalid [%d]", o->ps);
   const bool refine = o->wr > 0;
+  if (int rc = stnls_check_geom(g, refine ? -1 : o->wt, "search_forward")) return rc;
   FwdParams P;
   P.q = q_cl; P.k = k_cl; P.flows = flows; P.dists = dists; P.inds = inds; P.kselect = kselect; P.reflect = reflect;
   P.g = *g; P.o = *o;

@@ -212,12 +212,12 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
     else mine = group_params<INT, REFINE>(P, c, g0 + min(lane, nbg - 1));
     int my_ag = 0;
     if (REFINE && anchored) my_ag = refine_group_anchor<CC>(P, c, mine, g0 + min(lane, nbg - 1));
-    if (lane < nbg) sts1(sb + (gfrb + lane) * 4, (unsigned)((mine.ok && inb(mine.t, g.T)) ? (mine.t - g.tk0) : -1));
+    if (lane < nbg) sts1(sb + (gfrb + lane) * 4, (unsigned)((mine.ok && resident(mine.t, g)) ? (mine.t - g.tk0) : -1));
     // raw mode is taken for this batch when every window in it is interior: valid frame, no reflection,
     // consecutive in-frame taps and the same interpolation weights at every lattice coordinate
     constexpr bool RAWOK = !INT && DIST == 0 && Q4T > 0 && (PS == 1 || (PS == 3 && Q4T == 4));
     bool useraw = RAWOK && C.raw && qfull &&
-                  (__ballot_sync(FULL_MASK, lane >= nbg || (mine.ok && inb(mine.t, g.T))) == FULL_MASK);
+                  (__ballot_sync(FULL_MASK, lane >= nbg || (mine.ok && resident(mine.t, g))) == FULL_MASK);
     // 1. axis tables: one 32-lane round per group (both axes, M <= 16) or per (group, axis)
     for (int rd = 0; rd < nbg * C.ax_rounds; rd++) {
       int gl, axis, m;
@@ -462,7 +462,7 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
         CC chh;
         if (INT) chh = (CC)((int)gp.ah + (int)s1c * (wi - (int)gp.offh));
         else chh = (CC)fmaf((float)s1c, (float)wi - (float)gp.offh, (float)gp.ah);
-        const bool rowok = tact && gp.ok && inb(gp.t, g.T) && inb(chh, g.kH);
+        const bool rowok = tact && gp.ok && resident(gp.t, g) && inb(chh, g.kH);
         const int mh0 = C.n1 * wi;
         const unsigned hm = lds1(sb + (mskb + gl * 2) * 4) >> mh0, wmask = lds1(sb + (mskb + gl * 2 + 1) * 4);
         const bool hfull = qfull && ((hm & C.rpat) == C.rpat);
@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(256, (PS == 3 && Q4T == 4) ? 2 : (Q4T == 0) ? 
         chh = (CC)fmaf((float)s1c, (float)wi - (float)gp.offh, (float)gp.ah);
         cww = (CC)fmaf((float)s1c, (float)wj - (float)gp.offw, (float)gp.aw);
       }
-      const bool cvalid = active && gp.ok && inb(gp.t, g.T) && inb(chh, g.kH) && inb(cww, g.kW);
+      const bool cvalid = active && gp.ok && resident(gp.t, g) && inb(chh, g.kH) && inb(cww, g.kW);
       const int mh0 = C.n1 * wi, mw0 = C.n1 * wj;
       const unsigned hm = lds1(sb + (mskb + gl * 2) * 4) >> mh0, wm = lds1(sb + (mskb + gl * 2 + 1) * 4) >> mw0;
       const unsigned Tc = sb + (Tb + gl * C.GS4 + mh0 * C.Mp + mw0) * 16;

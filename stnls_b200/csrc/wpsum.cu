@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(128) wpsum_fwd_kernel(const __grid_constant__ 
           n0 = bnd(n0, g.T); n1 = bnd(n1, H); n2 = bnd(n2, W);
           n1 += d; n2 += e;
           if (o.reflect_bounds) { n1 = bnd(n1, H); n2 = bnd(n2, W); }
-          if (!(inb(n0, g.T) && inb(n1, H) && inb(n2, W))) continue;
+          if (!(resident(n0, g) && inb(n1, H) && inb(n2, W))) continue;
           const float4 pix = ldg4(vb + (int64_t)(n0 - g.tk0) * vfs + ((int64_t)n1 * W + n2) * g.Fp);
           acc.x += weight * pix.x; acc.y += weight * pix.y; acc.z += weight * pix.z; acc.w += weight * pix.w;
         } else {
@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(128) wpsum_fwd_kernel(const __grid_constant__ 
           n0 = bnd(n0, g.T); n1 = bnd(n1, H); n2 = bnd(n2, W);
           n1 += (float)d; n2 += (float)e;
           if (o.reflect_bounds) { n1 = bnd(n1, H); n2 = bnd(n2, W); }
-          if (!(inb(n0, g.T) && inb(n1, H) && inb(n2, W))) continue;
+          if (!(resident(n0, g) && inb(n1, H) && inb(n2, W))) continue;
           const Taps tp = make_taps(n1, n2, H, W);
           const float4 pix = interp4(vb - c4 + (int64_t)((int)n0 - g.tk0) * vfs, tp, W, g.Fp, c4);
           acc.x += weight * pix.x; acc.y += weight * pix.y; acc.z += weight * pix.z; acc.w += weight * pix.w;
@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(512) wpsum_fwd_tile_kernel(const __grid_consta
         int n0 = t + y0, c1 = rh + y1, c2 = rw + y2;
         if (!((abs(c1) < 1e7) && (abs(c2) < 1e7))) continue;
         n0 = bnd(n0, g.T); c1 = bnd(c1, H); c2 = bnd(c2, W);
-        if (!inb(n0, g.T)) continue;
+        if (!resident(n0, g)) continue;
         const float* vf = vb + (int64_t)(n0 - g.tk0) * vfs;
 #pragma unroll
         for (int pi = 0; pi < 3; pi++) {
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(512) wpsum_fwd_tile_kernel(const __grid_consta
         float n0 = (float)t + __int_as_float(y0), c1 = (float)rh + __int_as_float(y1), c2 = (float)rw + __int_as_float(y2);
         if (!((fabsf(c1) < 1e7) && (fabsf(c2) < 1e7))) continue;
         n0 = bnd(n0, g.T); c1 = bnd(c1, H); c2 = bnd(c2, W);
-        if (!inb(n0, g.T)) continue;
+        if (!resident(n0, g)) continue;
         const float* vf = vb + (int64_t)((int)n0 - g.tk0) * vfs;
         // interior neighbour: all 9 patch pixels unreflected, their taps inside one 4x4 footprint
         const int hh = __float2int_rz(c1 + (float)po), ww = __float2int_rz(c2 + (float)po);
@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
       int n0 = t + f[0], c1 = rh + f[1], c2 = rw + f[2];
       if (!((abs(c1) < 1e7) && (abs(c2) < 1e7))) return;
       n0 = bnd(n0, g.T); c1 = bnd(c1, H); c2 = bnd(c2, W);
-      if (!inb(n0, g.T)) return;
+      if (!resident(n0, g)) return;
       const float* vf = vb + (int64_t)(n0 - g.tk0) * vfs;
       float* gvf = gvb + (int64_t)(n0 - g.tk0) * vfs;
       for (int pi = 0; pi < o.ps; pi++) {
@@ -341,7 +341,7 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
       c1 = bnd(c1, H);
       const int sW0 = inb(c2, W) ? 1 : -1;
       c2 = bnd(c2, W);
-      if (!inb(n0, g.T)) return;
+      if (!resident(n0, g)) return;
       const int nti = (int)n0;
       const float* vf = vb + (int64_t)(nti - g.tk0) * vfs;
       float* gvf = gvb + (int64_t)(nti - g.tk0) * vfs;
@@ -421,7 +421,7 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
     float n0 = (float)t + f[0], c1 = (float)rh + f[1], c2 = (float)rw + f[2];
     // centre inside the frame (no reflection) and every tap of the 3x3 patch inside a 4x4 footprint
     n0 = bnd(n0, g.T);
-    bool ok = inb(n0, g.T) && (c1 >= 0) && (c2 >= 0) && (c1 <= (float)(H - 1)) && (c2 <= (float)(W - 1));
+    bool ok = resident(n0, g) && (c1 >= 0) && (c2 >= 0) && (c1 <= (float)(H - 1)) && (c2 <= (float)(W - 1));
     const int h0 = __float2int_rz(c1 + (float)po), w0 = __float2int_rz(c2 + (float)po);
     float gh[3][2], gw[3][2];
 #pragma unroll
@@ -485,7 +485,7 @@ int agg_check(const stnls_geom* g, const stnls_agg_opts* o, const char* who) {
   STNLS_REQUIRE(g->Fp % 4 == 0 && g->Fp >= g->F, "%s: Fp must be a multiple of 4 and >= F", who);
   STNLS_REQUIRE(g->qH == g->kH && g->qW == g->kW, "%s: output size must equal input size", who);
   STNLS_REQUIRE(o->ps > 0 && o->stride0 > 0 && o->K >= 0, "%s: bad ps/stride0/K", who);
-  return STNLS_OK;
+  return stnls_check_geom(g, -1, who);
 }
 
 }  // namespace
