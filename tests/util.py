@@ -19,10 +19,12 @@ def make_flows(B, HD_f, T, nF, nH, nW, kind, seed=1):
     return th.rand(shape, generator=g) / 2 + th.randint(-3, 3, shape, generator=g) + 0.2
 
 
-def assert_topk_equal(d, i, d_ref, i_ref, exact, atol=1e-4, rtol=1e-4, what=""):
+def assert_topk_equal(d, i, d_ref, i_ref, exact, atol=1e-4, rtol=1e-4, what="", last_slot_clear=True):
     """Compare (dists, inds) of a top-K search.  exact: bit-equal dists and equal indices.
     Otherwise dists within tolerance and indices equal wherever the neighbouring distances are
-    separated by more than the tolerance (near-ties may legitimately swap)."""
+    separated by more than the tolerance (near-ties may legitimately swap).  last_slot_clear=False: the last kept
+    slot is not called clearly separated -- the distance of the best candidate that was NOT kept is unknown, and a
+    near-tie across that boundary swaps which of the two is kept (million-query cases hit a few of those)."""
     d, i, d_ref, i_ref = d.cpu(), i.cpu(), d_ref.cpu(), i_ref.cpu()
     assert d.shape == d_ref.shape, (what, d.shape, d_ref.shape)
     assert i.shape == i_ref.shape, (what, i.shape, i_ref.shape)
@@ -42,6 +44,8 @@ def assert_topk_equal(d, i, d_ref, i_ref, exact, atol=1e-4, rtol=1e-4, what=""):
     gap_next = th.full_like(d_ref, float("inf"))
     gap_prev[..., 1:] = (d_ref[..., 1:] - d_ref[..., :-1]).abs()
     gap_next[..., :-1] = gap_prev[..., 1:]
+    if not last_slot_clear:
+        gap_next[..., -1] = 0.0
     clear = fin & (gap_prev > 4 * tol) & (gap_next > 4 * tol)
     diff = (i.float() - i_ref.float()).abs().amax(-1)
     bad = clear & (diff > 1e-3)
