@@ -13,10 +13,11 @@
 //     to the <= ps*ps candidates that cover it: per (query, frame, channel) ~(ws+ps)^2 LDS.32 and
 //     4 (ws+ps-1)^2 + (1|2) ps^2 ws^2 flops -- no interpolated table in shared memory, no per-query global loads;
 //   * the per-channel partial sums of finished candidate rows are transposed through a small per-warp scratch,
-//     one lane per candidate sums the Fp partials and stores the candidate's ordered key in the query's POOL in
-//     shared memory; the K best are then extracted by the query's Fp lanes with butterfly shuffles (min key, ties
-//     to the lower candidate index) into a sorted list -- once after the last frame slot when the pool holds all
-//     L candidates (small windows), else after every frame slot (list + that slot's ws*ws candidates);
+//     one lane per candidate sums the Fp partials; candidates that are not worse than the query's K-th best so far
+//     are APPENDED (ballot + popc slot) to the query's 64-entry pool in shared memory.  Only when a pool is about to
+//     overflow, and once after the last frame slot, the query's Fp lanes compact it to the K best, sorted
+//     (tile_merge: lanes sort their share in registers, K butterfly-min rounds, ties to the lower candidate index)
+//     and the K-th key becomes the new admission threshold -- about three compactions per query;
 //   * stride1 = 0.5: candidates split by the parity of their window row / column into four integer-spaced
 //     sub-windows, each with its own fractional phase.
 // A query whose window does not fit the staged box for some frame slot (flows that vary by more than the budget
@@ -39,9 +40,6 @@ struct TileCfg {
   int nbuf;                // box buffers (2: the next frame slot loads while this one is searched)
   int tiles_h, tiles_w;
   int LK;                  // entries of the per-query list (K, or K-1 when slot 0 is the anchor)
-  int NP;                  // candidate slots of the pool behind the list: L (one merge at the end) or ws*ws (per frame slot)
-  int per_frame;           // 1: merge after every frame slot
-  int PLs;                 // pool stride per query, in keys
   int QT;                  // staged query tile: QT x QT pixels
   int off_qt;
   int box_bytes;           // one buffer, multiple of 128
@@ -160,6 +158,61 @@ __device__ __forceinline__ void tile_core(const float* __restrict__ bp, const in
   }
 }
 
+// ---- pool compaction: the K best of a query's pool, sorted, to the head of the pool ------------------------------
+// Called by whole warps; each sub-group of FP lanes works on its own query (pk/px/cnt/thr are that query's) and the
+// butterflies use xor offsets < FP under the full mask.  Deliberately NOT inlined: it runs a few times per query,
+// from inside the unrolled core, and must not add to the core's register pressure.
+constexpr int TILE_CAP = 64;   // pool entries per query
+
+template <int FP>
+__device__ __noinline__ void tile_merge(unsigned* pk, int* px, int* cnt_ptr, unsigned* thr_ptr, const int LK, const int chl) {
+  constexpr int E = TILE_CAP / FP;
+  const int cnt = *cnt_ptr;
+  unsigned k[E];
+  int x[E];
+#pragma unroll
+  for (int j = 0; j < E; j++) {
+    const int e = chl + j * FP;
+    k[j] = (e < cnt) ? pk[e] : 0xffffffffu;
+    x[j] = (e < cnt) ? px[e] : 0x7fffffff;
+  }
+  __syncwarp();
+  // this lane's share, ascending by (key, candidate index): odd-even transposition network
+#pragma unroll
+  for (int r = 0; r < E; r++) {
+#pragma unroll
+    for (int a = (r & 1); a + 1 < E; a += 2) {
+      const bool sw = (k[a] > k[a + 1]) || (k[a] == k[a + 1] && x[a] > x[a + 1]);
+      const unsigned tk = sw ? k[a + 1] : k[a], uk = sw ? k[a] : k[a + 1];
+      const int tx = sw ? x[a + 1] : x[a], ux = sw ? x[a] : x[a + 1];
+      k[a] = tk; k[a + 1] = uk; x[a] = tx; x[a + 1] = ux;
+    }
+  }
+  unsigned last = 0xffffffffu;
+  for (int kk = 0; kk < LK; kk++) {
+    unsigned m = k[0];
+#pragma unroll
+    for (int off = FP / 2; off > 0; off >>= 1) m = min(m, __shfl_xor_sync(FULL_MASK, m, off));
+    unsigned wi = (k[0] == m) ? (unsigned)x[0] : 0x7fffffffu;
+#pragma unroll
+    for (int off = FP / 2; off > 0; off >>= 1) wi = min(wi, __shfl_xor_sync(FULL_MASK, wi, off));
+    if (chl == 0) { pk[kk] = m; px[kk] = (int)wi; }
+    last = m;
+    const bool won = (m != 0xffffffffu) && (k[0] == m) && (x[0] == (int)wi);
+#pragma unroll
+    for (int j = 0; j + 1 < E; j++) {
+      k[j] = won ? k[j + 1] : k[j];
+      x[j] = won ? x[j + 1] : x[j];
+    }
+    if (won) { k[E - 1] = 0xffffffffu; x[E - 1] = 0x7fffffff; }
+  }
+  if (chl == 0) {
+    *cnt_ptr = min(cnt, LK);
+    *thr_ptr = (cnt >= LK) ? last : 0xffffffffu;   // admission threshold: the K-th best key once K candidates exist
+  }
+  __syncwarp();
+}
+
 // rows of finished candidates handed over per flush: whole small windows at once, single rows of wide ones
 __host__ __device__ constexpr int tile_flush_rows(int WH, int WW) {
   return (WH * WW <= 16) ? WH : (2 * WW <= 16 && WH >= 2) ? 2 : 1;
@@ -195,8 +248,8 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
   // ---- shared memory ----
   float* const box0 = reinterpret_cast<float*>(smem);
   float4* const desc = reinterpret_cast<float4*>(smem + C.off_desc);       // [W_t][64]: (bh, bw, masks, -)
-  unsigned* const poolk = reinterpret_cast<unsigned*>(smem + C.off_pk);    // [64][PLs]: list keys [0,LK), then candidate keys
-  int* const pooli = reinterpret_cast<int*>(smem + C.off_pi);              // [64][32]: candidate index of the list entries
+  unsigned* const poolk = reinterpret_cast<unsigned*>(smem + C.off_pk);    // [64][TILE_CAP] pool: ordered keys ...
+  int* const pooli = reinterpret_cast<int*>(smem + C.off_pi);              // [64][TILE_CAP] ... and candidate indices
   float* const qt = reinterpret_cast<float*>(smem + C.off_qt);             // [QT][QT][FP] query pixels (reflected at the border)
   float* const scr = reinterpret_cast<float*>(smem + C.off_scr) + warp * C.scr_warp + sub * C.q_stride;
   int* const misc = reinterpret_cast<int*>(smem + C.off_misc);
@@ -206,10 +259,12 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
   int* const state = origin + TILE_MAXWT * 2;            // [64]: 0 searched here, 1 deferred to direct_query, 2 outside the grid
   int* const a_nls = state + TILE_NQ;                    // [64] anchor slot of the query
   float* const adist = reinterpret_cast<float*>(a_nls + TILE_NQ);   // [64] distance of the anchor candidate
+  int* const pcnt = a_nls + 2 * TILE_NQ;                 // [64] pool entries in use
+  unsigned* const pthr = reinterpret_cast<unsigned*>(pcnt + TILE_NQ);   // [64] admission threshold (ordered key)
   float* const akey = reinterpret_cast<float*>(smem + C.off_akey);   // [W_t][64] (anchored only)
   int* const apos = reinterpret_cast<int*>(smem + C.off_apos);
   const unsigned mbar0 = (unsigned)__cvta_generic_to_shared(misc);
-  const int LK = C.LK, PLs = C.PLs;
+  const int LK = C.LK;
 
   auto query_ctx = [&](int ql, QueryCtx& c) {
     c.b = b; c.hd = hd; c.n = n; c.t = t; c.tl = tl;
@@ -227,12 +282,13 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
     state[tid] = query_ctx(tid, c) ? 0 : 2;
     adist[tid] = invalid;
     a_nls[tid] = 0;
+    pcnt[tid] = 0;
+    pthr[tid] = 0xffffffffu;
   }
   if (tid < W_t) {
     int* s = stats + tid * 8;
     s[0] = s[3] = 0x7fffffff; s[1] = s[4] = -0x7fffffff; s[2] = s[5] = s[6] = 0;
   }
-  for (int i = tid; i < TILE_NQ * PLs; i += TILE_THREADS) poolk[i] = 0xffffffffu;   // empty
   {
     const float* const qfr = P.q + ((int64_t)n * g.Tq + tl) * (int64_t)g.qH * g.qW * FP;
     for (int i = tid; i < C.QT * C.QT * (FP / 4); i += TILE_THREADS) {
@@ -344,65 +400,6 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
 
   const int rowpitch = C.BW * FP;
 
-  // K best of a query's pool -> sorted list at the head of the pool.  Executed by the query's FP lanes; the
-  // butterflies use xor offsets < FP, so every sub-group of the warp reduces on its own under the full mask.
-  // npool: slots in use (list + candidate slots); slot p >= LK holds the candidate with index base + (p - LK)
-  // after the anchor swap of slot 0 (idx_of).
-  auto merge = [&](const int ql, const int npool, const int base, const int an) {
-    unsigned* const pk = poolk + ql * PLs;
-    int* const pi_ = pooli + ql * 32;
-    auto idx_of = [&](int p) {
-      if (p < LK) return pi_[p];
-      const int pos = base + (p - LK);
-      return anchored ? ((pos == 0) ? an : (pos == an) ? 0 : pos) : pos;
-    };
-    unsigned bk, bk2;   // this lane's best two unused entries: key, candidate index, pool slot
-    int bi, bi2, bp, bp2;
-    auto scan2 = [&]() {
-      bk = bk2 = 0xffffffffu;
-      bi = bi2 = 0x7fffffff;
-      bp = bp2 = 0;
-      for (int p2 = chl; p2 < npool; p2 += FP) {
-        const unsigned kv = pk[p2];
-        if (kv == 0xffffffffu) continue;
-        const int iv = idx_of(p2);
-        if (kv < bk || (kv == bk && iv < bi)) { bk2 = bk; bi2 = bi; bp2 = bp; bk = kv; bi = iv; bp = p2; }
-        else if (kv < bk2 || (kv == bk2 && iv < bi2)) { bk2 = kv; bi2 = iv; bp2 = p2; }
-      }
-    };
-    scan2();
-    bool have2 = true;
-    unsigned rk[NS];
-    int ri[NS];
-#pragma unroll
-    for (int s = 0; s < NS; s++) { rk[s] = 0xffffffffu; ri[s] = 0x7fffffff; }
-    for (int kk = 0; kk < LK; kk++) {
-      unsigned m = bk;
-#pragma unroll
-      for (int off = FP / 2; off > 0; off >>= 1) m = min(m, __shfl_xor_sync(FULL_MASK, m, off));
-      unsigned wi = (bk == m) ? (unsigned)bi : 0x7fffffffu;
-#pragma unroll
-      for (int off = FP / 2; off > 0; off >>= 1) wi = min(wi, __shfl_xor_sync(FULL_MASK, wi, off));
-      if (chl == (kk & (FP - 1))) {
-#pragma unroll
-        for (int s = 0; s < NS; s++)
-          if (s == kk / FP) { rk[s] = m; ri[s] = (int)wi; }
-      }
-      if (m != 0xffffffffu && bk == m && bi == (int)wi) {   // this lane's entry won: retire it
-        pk[bp] = 0xffffffffu;
-        if (have2) { bk = bk2; bi = bi2; bp = bp2; have2 = false; }
-        else { scan2(); have2 = true; }
-      }
-    }
-    __syncwarp();
-#pragma unroll
-    for (int s = 0; s < NS; s++) {
-      const int e = s * FP + chl;
-      if (e < LK) { pk[e] = rk[s]; pi_[e] = ri[s]; }
-    }
-    __syncwarp();
-  };
-
   for (int st = 0; st < W_t; st++) {
     const int buf = st % C.nbuf;
     const unsigned par = (unsigned)(st / C.nbuf) & 1u;
@@ -426,9 +423,6 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
       }
       __syncthreads();
     }
-    // pool slot of this frame slot's candidate 0
-    const int slot0 = LK + (C.per_frame ? 0 : st * WS * WS);
-
     for (int pass = 0; pass < TILE_NQ / (8 * QW); pass++) {
       const int ql = (pass * 8 + warp) * QW + sub;
       const bool active = state[ql] == 0;
@@ -436,7 +430,10 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
       const unsigned masks = __float_as_uint(dsc.z);
       const unsigned hm = masks & 0xffffu, wm = masks >> 16;
       const int an = a_nls[ql];
-      unsigned* const pk = poolk + ql * PLs + slot0;
+      unsigned* const pk = poolk + ql * TILE_CAP;
+      int* const px = pooli + ql * TILE_CAP;
+      int cnt = pcnt[ql];            // register copies, uniform inside the sub-group
+      unsigned thr = pthr[ql];
       // query patch, this lane's channel
       float qv[PS * PS];
       {
@@ -465,6 +462,8 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
 #pragma unroll
           for (int m = 0; m < (G * WW + FP - 1) / FP; m++) {
             const int v = chl + m * FP;
+            unsigned key = 0xffffffffu;
+            int eff = 0;
             if (v < nv) {
               const float4* sp = reinterpret_cast<const float4*>(scr + v * C.cand_pitch);
               float d = 0.f;
@@ -476,17 +475,30 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
               const int vi = v / WW, vj = v - vi * WW;
               const int wi = eh + STEP * (ibase + vi), wj = ew + STEP * vj;
               if (!((hm >> wi) & (wm >> wj) & 1u)) d = invalid;
-              const int sl = wi * WS + wj;          // slot inside the frame slot's window
-              unsigned key = min(f2ord_t(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu);
-              if (anchored) {
-                const int pos = st * WS * WS + sl;
-                if (pos == an) {                    // the anchor: reported in slot 0, not a member of the list
-                  adist[ql] = d;
-                  key = 0xffffffffu;
-                }
+              eff = st * WS * WS + wi * WS + wj;
+              key = min(f2ord_t(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu);
+              if (anchored) {   // anchor swap (anchor_self_kernel.cu:101-113): the anchor is reported in slot 0 and is not
+                                // a member of the list; the candidate it displaces from position 0 takes its index
+                if (eff == an) { adist[ql] = d; key = 0xffffffffu; }
+                else if (eff == 0) eff = an;
               }
-              if (active) pk[sl] = key;
             }
+            // room for one entry per lane?  (rare; warp-uniform, each sub-group compacts its own pool)
+            if (__any_sync(FULL_MASK, cnt + FP > TILE_CAP)) {
+              if (chl == 0) pcnt[ql] = cnt;
+              __syncwarp();
+              tile_merge<FP>(pk, px, pcnt + ql, pthr + ql, LK, chl);
+              cnt = pcnt[ql];
+              thr = pthr[ql];
+            }
+            const bool pass = active && key <= thr && key != 0xffffffffu;
+            const unsigned mine = __ballot_sync(FULL_MASK, pass) & submask;
+            if (pass) {
+              const int slot = cnt + __popc(mine & ((1u << lane) - 1u));
+              pk[slot] = key;
+              px[slot] = eff;
+            }
+            cnt += __popc(mine);
           }
           __syncwarp();
         };
@@ -501,7 +513,7 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
         run_window(std::integral_constant<int, WO>(), std::integral_constant<int, WE>(), 1, 0);
         run_window(std::integral_constant<int, WO>(), std::integral_constant<int, WO>(), 1, 1);
       }
-      if (C.per_frame) merge(ql, LK + WS * WS, st * WS * WS, an);
+      if (chl == 0) pcnt[ql] = cnt;
     }
     __syncthreads();
     if (tid == 0 && st + C.nbuf < W_t) issue(st + C.nbuf);
@@ -512,7 +524,8 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
   for (int pass = 0; pass < TILE_NQ / (8 * QW); pass++) {
     const int ql = (pass * 8 + warp) * QW + sub;
     const int an = a_nls[ql];
-    if (!C.per_frame) merge(ql, LK + W_t * WS * WS, 0, an);
+    __syncwarp();
+    tile_merge<FP>(poolk + ql * TILE_CAP, pooli + ql * TILE_CAP, pcnt + ql, pthr + ql, LK, chl);
     if (state[ql] != 0) continue;
     QueryCtx c;
     query_ctx(ql, c);
@@ -528,8 +541,8 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
     for (int s = 0; s < NS; s++) {
       const int e = s * FP + chl;
       if (e >= LK) continue;
-      const unsigned mk = poolk[ql * PLs + e];
-      const int mi = pooli[ql * 32 + e];
+      const unsigned mk = poolk[ql * TILE_CAP + e];
+      const int mi = pooli[ql * TILE_CAP + e];
       if (mk == 0xffffffffu) continue;   // cannot happen: K <= number of candidates
       int gq = mi / (WS * WS), sl = mi - gq * (WS * WS);
       if (anchored && mi == an) { gq = 0; sl = 0; }   // the entry displaced from slot 0 by the anchor swap

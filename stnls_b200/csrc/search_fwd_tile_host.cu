@@ -33,21 +33,15 @@ EncodeTiledFn encode_tiled() {
 int round_up(int x, int m) { return (x + m - 1) / m * m; }
 
 // shared memory one CTA needs with `nbuf` box buffers; fills the carve
-int carve(const FwdParams& P, TileCfg& C, int nbuf, int per_frame) {
+int carve(const FwdParams& P, TileCfg& C, int nbuf) {
   const int Fp = P.g.Fp, QW = 32 / Fp;
   C.nbuf = nbuf;
-  C.per_frame = per_frame;
   C.box_tx = C.BH * C.BW * Fp * 4;
   C.box_bytes = round_up(C.box_tx, 128);
   int off = nbuf * C.box_bytes;
   C.off_desc = off; off += TILE_NQ * P.W_t * 16;
-  // pool: list + candidate keys per query; the stride is odd in 16-byte units so the sub-groups of a warp hit
-  // different banks
-  C.NP = C.per_frame ? P.o.ws * P.o.ws : P.L;
-  C.PLs = round_up(C.LK + C.NP, 4);
-  if (!((C.PLs / 4) & 1)) C.PLs += 4;
-  C.off_pk = off; off += TILE_NQ * C.PLs * 4;
-  C.off_pi = off; off += TILE_NQ * 32 * 4;
+  C.off_pk = off; off += TILE_NQ * TILE_CAP * 4;   // per-query pool: keys ...
+  C.off_pi = off; off += TILE_NQ * TILE_CAP * 4;   // ... and candidate indices
   C.QT = (TILE_TQ - 1) * P.o.stride0 + P.o.ps;
   C.off_qt = off; off += round_up(C.QT * C.QT * Fp * 4, 16);
   // transpose scratch: candidates of one flush x (Fp + 4) floats per query; the query stride keeps the sub-groups of a
@@ -65,7 +59,7 @@ int carve(const FwdParams& P, TileCfg& C, int nbuf, int per_frame) {
   while ((C.q_stride & 31) != (Fp & 31)) C.q_stride++;
   C.scr_warp = QW * C.q_stride;
   C.off_scr = off; off += (TILE_THREADS / 32) * C.scr_warp * 4;
-  C.off_misc = off; off += (4 + TILE_MAXWT * 8 + TILE_MAXWT * 2 + 3 * TILE_NQ) * 4;
+  C.off_misc = off; off += (4 + TILE_MAXWT * 8 + TILE_MAXWT * 2 + 5 * TILE_NQ) * 4;
   C.off_akey = off; off += P.o.anchor_self ? TILE_NQ * P.W_t * 4 : 0;
   C.off_apos = off; off += P.o.anchor_self ? TILE_NQ * P.W_t * 4 : 0;
   C.smem_bytes = round_up(off, 128);
@@ -108,21 +102,15 @@ int launch_tile(const FwdParams& P, cudaStream_t st) {
   C.tiles_w = (g.nW + TILE_TQ - 1) / TILE_TQ;
   const int64_t blocks = (int64_t)C.tiles_h * C.tiles_w * g.Tq * g.B * g.HD;
   if (blocks <= 0 || blocks >= 2147483647LL) return 0;
-  // shared-memory plan, in order of preference (two CTAs per SM = 113 KB each):
-  //   all candidates pooled (one extraction at the end) + two box buffers, the same with one buffer,
-  //   per-frame-slot extraction + two buffers, + one buffer; then the same list allowing one CTA per SM
+  // two box buffers (the next frame slot loads while this one is searched) when two CTAs per SM still fit
+  // (113 KB each), else one buffer; one CTA per SM as the last resort
   const char* env_nb = getenv("STNLS_FWD_TILE_NBUF");
-  const char* env_pf = getenv("STNLS_FWD_TILE_PERFRAME");
   bool planned = false;
-  for (int limit = 113 * 1024; limit <= 227 * 1024 && !planned; limit += 114 * 1024) {
-    for (int pf = 0; pf < 2 && !planned; pf++) {
-      if (env_pf && atoi(env_pf) != pf) continue;
-      for (int nb = 2; nb >= 1 && !planned; nb--) {
-        if (env_nb && atoi(env_nb) != nb) continue;
-        if (carve(P, C, nb, pf) + 1024 <= limit) planned = true;
-      }
+  for (int limit = 113 * 1024; limit <= 227 * 1024 && !planned; limit += 114 * 1024)
+    for (int nb = 2; nb >= 1 && !planned; nb--) {
+      if (env_nb && atoi(env_nb) != nb) continue;
+      if (carve(P, C, nb) + 1024 <= limit) planned = true;
     }
-  }
   if (!planned) return 0;
 
   // ---- tensor map: k_cl as (Fp, kW, kH, N*Tk), box (Fp, BW, BH, 1), zero fill outside ----
