@@ -30,6 +30,9 @@ if ROOT not in sys.path:
 import torch as th  # noqa: E402
 
 WORKLOADS = {
+    # README example on CPU and GPU (configs[0], C1): int, search + agg FORWARD only
+    "c1": dict(B=1, T=5, F=16, H=64, W=64, HD=2, ws=5, wt=2, ps=3, K=10, stride0=1, stride1=1.0,
+               dist_type="l2", self_action="anchor", itype="int", scale=10.0, passes="fwd"),
     # README example on 1 B200 (BASELINE.json configs[1])
     "c2": dict(B=1, T=5, F=16, H=128, W=128, HD=2, ws=5, wt=2, ps=3, K=10, stride0=1, stride1=0.5,
                dist_type="l2", self_action="anchor", itype="float", scale=10.0),
@@ -42,18 +45,30 @@ WORKLOADS = {
     # 1080p slice per rank (configs[3], C4): T frames PER RANK
     "c4": dict(B=1, T=7, F=64, H=1080, W=1920, HD=4, ws=9, wt=3, ps=3, K=20, stride0=1, stride1=1.0,
                dist_type="prod", self_action=None, itype="float", scale=10.0),
+    # the 1080p block every line carries (configs[3], C4): 8 frames PER RANK of full 1080x1920; N ranks hold
+    # B*T = 8N frames (N=8: B=2, T=32, ranks 0-3 batch 0, ranks 4-7 batch 1), fwd+bwd in chunks of 2 frames
+    "c4_1080p": dict(B=1, T=8, F=64, H=1080, W=1920, HD=4, ws=9, wt=3, ps=3, K=20, stride0=1, stride1=1.0,
+                     dist_type="prod", self_action=None, itype="float", scale=10.0, Tmax=32, chunk=2),
+    # RefineSearch 4K (configs[4], C5): 4 frames PER RANK (N=8: T=32); BASELINE.json leaves ps / nheads / wt open:
+    # ps=3 (README), nheads=1 (ctor default), wt=1 -- SURVEY.md 8d.  Refine forward + aggregation forward+backward
+    "c5": dict(B=1, T=4, F=32, H=2160, W=3840, HD=1, ws=3, wt=1, wr=3, Ks=30, K=30, ps=3, stride0=2, stride1=1.0,
+               dist_type="l2", self_action=None, itype="float", scale=10.0, Tmax=32, refine=True,
+               passes="refine fwd + agg fwd+bwd"),
 }
 
 
 def describe(wl, name, world):
     c = dict(wl)
-    c["workload"] = {"c2": "README example (BASELINE configs[1]): search+agg fwd+bwd",
+    c["workload"] = {"c1": "README example, int (BASELINE configs[0]): search+agg forward",
+                     "c4_1080p": "1080p (BASELINE configs[3]): 8 frames per rank, search+agg fwd+bwd",
+                     "c5": "RefineSearch 4K (BASELINE configs[4]): 4 frames per rank, refine fwd + agg fwd+bwd",
+                     "c2": "README example (BASELINE configs[1]): search+agg fwd+bwd",
                      "c3": "RVRT-style GDA replacement (BASELINE configs[2])",
                      "c4": "1080p slice (BASELINE configs[3])",
                      "c4s": "1080p config at quarter resolution (tuning stand-in)"}[name]
     c["name"] = name
     c["T_global"] = wl["T"] * world
-    c["sharding"] = "single GPU" if world == 1 else f"T sharded over {world} ranks, NCCL halo exchange of k,v"
+    c["sharding"] = "single GPU" if world == 1 else f"frames sharded over {world} ranks, halo exchange of k,v (see `halo`)"
     c["l2_policy"] = "L2 flushed (512 MiB write) before every timed step"
     return c
 
@@ -61,7 +76,7 @@ def describe(wl, name, world):
 def candidates_per_step(wl, world=1):
     nH = (wl["H"] - 1) // wl["stride0"] + 1
     nW = (wl["W"] - 1) // wl["stride0"] + 1
-    L = (2 * wl["wt"] + 1) * wl["ws"] ** 2
+    L = wl["Ks"] * wl["wr"] ** 2 if wl.get("refine") else (2 * wl["wt"] + 1) * wl["ws"] ** 2
     return wl["B"] * wl["HD"] * wl["T"] * world * nH * nW * L
 
 
@@ -96,14 +111,31 @@ def algorithmic(wl, Tk):
     W_t, K, ps = 2 * wl["wt"] + 1, wl["K"], wl["ps"]
     N = B * HD
     vq, vk = N * T * Fh * H * W * 4, N * Tk * Fh * H * W * 4
-    flows = B * T * (W_t - 1) * 2 * nH * nW * 4
     dists = N * T * nH * nW * K * 4
     inds = dists * 3
-    cands = N * T * nH * nW * W_t * wl["ws"] ** 2
+    if wl.get("refine"):
+        flows = N * T * nH * nW * wl["Ks"] * 3 * 4
+        cands = N * T * nH * nW * wl["Ks"] * wl["wr"] ** 2
+        win = wl["wr"]
+    else:
+        flows = B * T * (W_t - 1) * 2 * nH * nW * 4
+        cands = N * T * nH * nW * W_t * wl["ws"] ** 2
+        win = wl["ws"]
     per_pix = (3 if wl["dist_type"] == "l2" else 2) + (0 if wl["itype"] == "int" else 8)
     flt = wl["itype"] != "int"
+    # flops the kernels actually execute per candidate: every lattice point of the window is interpolated ONCE (4 flops,
+    # separable) and then feeds up to ps*ps candidates (3 flops l2 / 2 prod) -- the SURVEY figure charges 8 flops of
+    # bilinear work per patch pixel of every candidate, which neither kernel performs
+    half = (not wl.get("refine")) and wl["stride1"] == 0.5 and flt
+    if half:
+        subs = [((win + 1) // 2, (win + 1) // 2), ((win + 1) // 2, win // 2), (win // 2, (win + 1) // 2), (win // 2, win // 2)]
+    else:
+        subs = [(win, win)]
+    lattice = sum((a + ps - 1) * (b + ps - 1) for a, b in subs)
+    exe = (4 * lattice if flt else 0) + (3 if wl["dist_type"] == "l2" else 2) * ps * ps * win * win
     return {
-        "search_forward": dict(bytes=vq + vk + flows + dists + inds, flops=cands * ps * ps * Fh * per_pix),
+        "search_forward": dict(bytes=vq + vk + flows + dists + inds, flops=cands * ps * ps * Fh * per_pix,
+                               flops_executed=cands // (win * win) * exe * Fh),
         # reads q,k,grad_dists,inds(,grad_inds,flows); writes grad_q, grad_k(, grad_flows)
         "search_backward": dict(bytes=2 * vq + 2 * vk + dists + inds + (inds + 2 * flows if flt else 0)),
         "wpsum_forward": dict(bytes=vk + dists + inds + vq),          # v, weights, inds -> out
@@ -414,6 +446,21 @@ def run_product(args):
         if flt:
             to_host("grad_flows", dev_in[3].grad, done)
 
+    # measured host link: one upload of a step's inputs and one download of as many bytes, every rank at the same time
+    barrier()
+    t0 = time.perf_counter()
+    tmp = [t.to(dev, non_blocking=True) for t in host]
+    th.cuda.synchronize()
+    h2d_gbs = h2d / (time.perf_counter() - t0) / 1e9
+    back = [th.empty(t.shape, dtype=t.dtype).pin_memory() for t in host]
+    barrier()
+    t0 = time.perf_counter()
+    for a_, b_ in zip(back, tmp):
+        a_.copy_(b_, non_blocking=True)
+    th.cuda.synchronize()
+    d2h_gbs = h2d / (time.perf_counter() - t0) / 1e9
+    del tmp, back
+
     # latency form
     lat_s = 0.0
     for i in range(args.warmup + args.steps):
@@ -516,8 +563,195 @@ def run_product(args):
         graph_ms = float(tt[2])
     return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
                 launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h, graph_ms=graph_ms, graph_note=graph_note,
-                per_graph=per_graph, unit=unit, lat_ms=lat_ms, e2e_from=e2e_from, e2e_eager_ms=e2e_eager_ms, numa=numa)
+                per_graph=per_graph, unit=unit, lat_ms=lat_ms, e2e_from=e2e_from, e2e_eager_ms=e2e_eager_ms, numa=numa,
+                h2d_gbs=h2d_gbs, d2h_gbs=d2h_gbs)
 
+
+
+# ------------------------------------------------------------------------------------------------
+#   blocks: further BASELINE configurations timed beside the main workload (device-resident inputs, CUDA events,
+#   L2 flushed between steps, max over ranks).  Inputs are generated ON the device (a 1080p rank holds 13 GB of video).
+# ------------------------------------------------------------------------------------------------
+
+def block_shape(wl, world):
+    """(B, T) of the whole job for a per-rank workload: wl['T'] frames per rank, clips of at most wl['Tmax'] frames"""
+    total = wl["T"] * world
+    T = min(wl.get("Tmax", total), total)
+    return total // T, T
+
+
+def device_inputs(wl, B, plan, dev, rank):
+    """owned frames of q,k,v,grad_out (+ flows) on the device; NLS flows as SURVEY.md 8d, refine offsets as 8d C5"""
+    g = th.Generator(device=dev).manual_seed(4321 + rank)
+    Tr, F, H, W, HD = plan.b - plan.a, wl["F"], wl["H"], wl["W"], wl["HD"]
+    nH, nW = (H - 1) // wl["stride0"] + 1, (W - 1) // wl["stride0"] + 1
+    q, k, v = [th.randn(B, Tr, F, H, W, device=dev, generator=g) for _ in range(3)]
+    gout = th.randn(B, HD, Tr, F // HD, H, W, device=dev, generator=g)
+    if wl.get("refine"):
+        fl = th.empty(B, HD, Tr, nH, nW, wl["Ks"], 3, device=dev)
+        dt = th.randint(-1, 2, fl[..., 0].shape, device=dev, generator=g)
+        tq = th.arange(plan.a, plan.b, device=dev).view(1, 1, Tr, 1, 1, 1)
+        fl[..., 0] = ((tq + dt).clamp(0, plan.T - 1) - tq).float()
+        fl[..., 1:] = th.randint(-8, 8, fl[..., 1:].shape, device=dev, generator=g).float()
+        fl[..., 1:] += th.rand(fl[..., 1:].shape, device=dev, generator=g) / 2 + 0.2
+    else:
+        shape = (B, 1, Tr, 2 * wl["wt"], 2, nH, nW)
+        fl = th.rand(shape, device=dev, generator=g) / 2 + th.randint(-3, 3, shape, device=dev, generator=g) + 0.2
+        if wl["itype"] == "int":
+            fl = fl.round()
+    return q, k, v, fl, gout
+
+
+def run_block(name, args, world, rank, dev, steps, warmup, groups=None):
+    """Time `steps` passes of workload `name` (see WORKLOADS) on this job's ranks.  Returns a dict on every rank."""
+    import torch.distributed as dist
+    import stnls_b200
+    from stnls_b200 import ops, parallel
+    wl = WORKLOADS[name]
+    B, T = block_shape(wl, world)
+    bslice, plan, ranks = parallel.flat_shard(B, T, wl["wt"], world, rank)
+    group = None
+    if len(ranks) > 1 and len(ranks) < world:
+        group = groups[B] if groups and B in groups else parallel.batch_groups(B, world, rank)
+        if groups is not None:
+            groups[B] = group
+    Bl = bslice.stop - bslice.start
+    kw = dict(nheads=wl["HD"], stride0=wl["stride0"], stride1=wl["stride1"], dist_type=wl["dist_type"],
+              self_action=wl["self_action"], itype=wl["itype"])
+    if wl.get("refine"):
+        search = stnls_b200.search.RefineSearch(wl["ws"], wl["wt"], wl["wr"], wl["K"], -1, wl["ps"], **kw)
+    else:
+        search = stnls_b200.search.NonLocalSearch(wl["ws"], wl["wt"], wl["ps"], wl["K"], **kw)
+    agg = stnls_b200.agg.WeightedPatchSum(ps=wl["ps"], stride0=wl["stride0"], itype=wl["itype"])
+    model = parallel.ShardedSearchAgg(search, agg, plan, scale=wl["scale"], group=group, halo=args.halo)
+    q, k, v, fl, gout = device_inputs(wl, Bl, plan, dev, rank)
+    passes = wl.get("passes", "fwd+bwd")
+    sign = -1.0 if wl["dist_type"] == "l2" else 1.0
+
+    def step():
+        if passes == "fwd":
+            with th.no_grad():
+                return model(q, k, v, fl)[0]
+        if wl.get("refine"):   # refine forward (no gradient) + aggregation forward + backward
+            with th.no_grad():
+                k_ext = parallel.halo_exchange(k, plan, group, model.peer, "k")
+                d, i = search(q, k_ext, fl, shard=plan.shard)
+                w = stnls_b200.normz.softmax.softmax_scaled(d, sign * wl["scale"])
+            vg, wg = v.detach().requires_grad_(True), w.requires_grad_(True)
+            v_ext = parallel.halo_exchange(vg, plan, group, model.peer, "v")
+            out = agg(v_ext, wg, i, shard=plan.shard)
+            (out * gout).sum().backward()
+            return out.detach()
+        return model.chunked_step(q, k, v, fl, gout, wl.get("chunk", plan.b - plan.a))[0]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        th.cuda.synchronize()
+
+    flush = th.empty(512 << 20, dtype=th.uint8, device=dev)
+    for _ in range(warmup):
+        out = step()
+    barrier()
+    assert bool(th.isfinite(out).all()), name + ": non-finite output"
+    del out
+    ops.TIMELINE = []
+    evs = []
+    barrier()
+    for _ in range(steps):
+        flush.zero_()
+        e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
+        e0.record()
+        step()
+        e1.record()
+        evs.append((e0, e1))
+    barrier()
+    timeline, ops.TIMELINE = ops.TIMELINE, None
+    ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    tt = th.tensor([ms], dtype=th.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms = float(tt[0])
+    peak_mem = th.cuda.max_memory_allocated(dev) / 2 ** 30
+    del q, k, v, fl, gout, flush
+    th.cuda.empty_cache()
+    cands = candidates_per_step(dict(wl, B=1), world)   # wl['T'] frames per rank, `world` ranks
+    kt = kernel_table(timeline, steps)
+    # algorithmic bytes per LAUNCH: a launch handles one chunk of frames (its own frames + the temporal halo of k / v)
+    ct = min(wl.get("chunk", plan.b - plan.a), plan.b - plan.a)
+    alg = algorithmic(dict(wl, B=Bl, T=ct), min(ct + 2 * wl["wt"], plan.fb - plan.fa))
+    for n_ in kt:
+        if n_ in alg and alg[n_]["bytes"]:
+            kt[n_]["alg_GBs"] = alg[n_]["bytes"] / (kt[n_]["ms_per_launch"] * 1e-3) / 1e9
+    cfg = {k_: wl[k_] for k_ in ("F", "H", "W", "HD", "ws", "wt", "ps", "K", "stride0", "stride1", "dist_type", "itype")}
+    if wl.get("refine"):
+        cfg.update(wr=wl["wr"], Ks=wl["Ks"], nheads=wl["HD"])
+    return {"workload": describe(wl, name, world)["workload"], "config": dict(cfg, B=B, T=T, frames_per_rank=wl["T"]),
+            "passes": passes, "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms,
+            "frames_per_s": B * T / (ms * 1e-3), "Gcandidates_per_s": cands / (ms * 1e-3) / 1e9,
+            "halo": model.halo_kind, "peak_device_GiB": round(peak_mem, 1),
+            "kernels": {n_: {"ms_per_step": round(v_["ms_per_step"], 4), "launches_per_step": v_["launches"] / steps,
+                             **({"alg_GBs": round(v_["alg_GBs"], 1)} if "alg_GBs" in v_ else {})} for n_, v_ in kt.items()},
+            "data": "synthetic, generated on the device", "l2_policy": "L2 flushed (512 MiB write) before every timed step"}
+
+
+def reference_cuda_on_b200(dev, budget_frames=4):
+    """the reference's OWN kernels (oracle/_ref, compiled from /root/reference/lib/csrc) through the
+    reference's stock call path (oracle/ref_cuda.py: non_local_search_*_forward -> anchor_self -> topk ->
+    gather_add_*; backward kernels included), timed with CUDA events on this GPU, outside every product timing.
+    C1 and C2 at full size; C3 on a 4-frame slice of one clip (its intermediates are 16 B per candidate)."""
+    try:
+        from oracle import ref_cuda
+        if not ref_cuda.available():
+            return {"unavailable": "oracle/_ref/stnls_cuda_ref*.so not present"}
+        ref_cuda.mod()
+    except Exception as exc:
+        return {"unavailable": f"{type(exc).__name__}: {exc}"[:160]}
+    res = {"what": "reference CUDA kernels (lib/csrc, unmodified but for .type()->.scalar_type()) driven as "
+                   "lib/stnls/search/impl/non_local_search.py + lib/stnls/agg/gather_add.py do; CUDA events, median of 3"}
+    for name in ("c1", "c2", "c3"):
+        wl = dict(WORKLOADS[name])
+        if name == "c3":
+            wl.update(B=1, T=budget_frames)
+        q, k, v, fl, gout = [t.to(dev) for t in make_inputs(wl, 0, 1, pin=False)]
+        kw = dict(nheads=wl["HD"], stride0=wl["stride0"], dist_type=wl["dist_type"], itype=wl["itype"])
+        flt = wl["itype"] == "float"
+        sign = -1.0 if wl["dist_type"] == "l2" else 1.0
+        bwd = wl.get("passes", "fwd+bwd") != "fwd"
+
+        def once():
+            d, i = ref_cuda.nls_forward(q, k, fl, wl["ws"], wl["wt"], wl["ps"], wl["K"], stride1=wl["stride1"],
+                                        self_action=wl["self_action"], **kw)
+            d.requires_grad_(bwd)
+            w = th.softmax(sign * wl["scale"] * d, -1)
+            out, counts = ref_cuda.gather_add_forward(v, w.detach(), i, wl["ps"], wl["stride0"], itype=wl["itype"])
+            if bwd:
+                gv, gw, gf = ref_cuda.gather_add_backward(gout, v, w.detach(), i, counts, wl["ps"], wl["stride0"],
+                                                          itype=wl["itype"])
+                w.backward(gw)
+                ref_cuda.search_backward(q, k, fl, d.grad, gf if flt else None, i, wl["wt"], wl["ps"], flows_grad=flt,
+                                         dists=d.detach(), **kw)
+            return out
+        try:
+            once()
+            th.cuda.synchronize()
+            ts = []
+            for _ in range(3):
+                e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
+                e0.record()
+                once()
+                e1.record()
+                e1.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            ms = sorted(ts)[1]
+            res[name] = {"ms_per_step": ms, "Gcandidates_per_s": candidates_per_step(wl) / (ms * 1e-3) / 1e9,
+                         "passes": wl.get("passes", "fwd+bwd"),
+                         "sample": "full size" if name != "c3" else f"{budget_frames}-frame slice of one clip (B=1)"}
+        except Exception as exc:
+            res[name] = {"failed": f"{type(exc).__name__}: {exc}"[:160]}
+        del q, k, v, fl, gout
+        th.cuda.empty_cache()
+    return res
 
 # ------------------------------------------------------------------------------------------------
 #   CPU arm: the C restatement of the reference kernels (oracle/, OpenMP over the host cores)
@@ -539,6 +773,8 @@ def cpu_pass(wl, crop, threads):
     sign = -1.0 if w["dist_type"] == "l2" else 1.0
     wts = th.softmax(sign * w["scale"] * d, -1)
     out, counts = ref.gather_add_forward(v, wts.detach(), i, w["ps"], w["stride0"], itype=w["itype"])
+    if wl.get("passes") == "fwd":
+        return candidates_per_step(w), time.perf_counter() - t0
     gv, gw, gf = ref.gather_add_backward(gout, v, wts.detach(), i, counts, w["ps"], w["stride0"], itype=w["itype"])
     wts.backward(gw)
     gi = gf if flt else None
@@ -609,6 +845,74 @@ def kernel_table(timeline, steps):
     return {n: dict(ms_total=t, launches=c, ms_per_launch=t / c, ms_per_step=t / steps) for n, (t, c) in agg.items()}
 
 
+def run_extras(args, r):
+    """After the main workload, on every rank: the 1080p block (always), the RefineSearch-4K block (N = 1 and 8), and --
+    single GPU only -- the measured fp32 FMA peak and the reference's own CUDA kernels on this GPU."""
+    if args.blocks == "none":
+        return {}
+    import stnls_b200  # noqa: F401
+    from stnls_b200 import ops
+    world, rank = r["world"], r["rank"]
+    dev = th.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    out = {}
+    groups = {}
+    for name, when in (("c4_1080p", True), ("c5", world in (1, 8))):
+        if not when or (args.blocks != "all" and name not in args.blocks.split(",")):
+            continue
+        try:
+            out[name] = run_block(name, args, world, rank, dev, steps=2, warmup=1, groups=groups)
+        except Exception as exc:   # a block must not take the headline line down with it
+            out[name] = {"failed": f"{type(exc).__name__}: {exc}"[:300]}
+            th.cuda.synchronize()
+            th.cuda.empty_cache()
+    if rank == 0:
+        out["fp32_fma_peak"] = {"tflops": ops.ffma_peak_tflops(dev), "how": "stnls_ffma_peak: 8 CTAs x 256 threads per SM, 16 "
+                                "independent FFMA chains x 4096 steps per thread, CUDA events, best of 5 (csrc/peak.cu)"}
+        if world == 1 and not args.no_cpu_baseline:
+            out["reference_cuda_on_b200"] = reference_cuda_on_b200(dev)
+    return out
+
+
+def main_block(args):
+    """--workload c1 / c4_1080p / c5: one line from the block runner (device-resident inputs; no e2e leg)."""
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not th.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product arm has no CPU path)")
+    th.cuda.set_device(local)
+    dev = th.device("cuda", local)
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        if world > 1:
+            dist.init_process_group("nccl", device_id=dev)
+        with ClockSampler(local) as clk:
+            blk = run_block(args.workload, args, world, rank, dev, args.steps, args.warmup)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    if rank == 0:
+        wl = WORKLOADS[args.workload]
+        line = {"metric": "search+agg throughput (" + blk["passes"] + ")", "value": blk["Gcandidates_per_s"],
+                "unit": "Gcandidates/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": blk["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": blk["data"], "config": dict(describe(wl, args.workload, world), **blk["config"]),
+                "frames_per_s": blk["frames_per_s"], "clocks": clk.summary(), "kernels": blk["kernels"],
+                "halo": blk["halo"], "peak_device_GiB": blk["peak_device_GiB"]}
+        if world == 1 and not args.no_cpu_baseline and not wl.get("refine") and wl["H"] <= 256:
+            cores = os.cpu_count() or 1
+            c, t, n, crop = cpu_sample(wl, cores)
+            line["cpu_baseline"] = {"value": c / t / 1e9, "unit": "Gcandidates/s", "cores": cores, "kind": "port",
+                                    "sample": f"{n} pass(es) on a {crop}x{crop} crop, oracle/stnls_oracle.c with OpenMP"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -618,6 +922,8 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--halo", default="auto", choices=["auto", "peer", "nccl"])
+    ap.add_argument("--blocks", default="all",
+                    help="extra blocks after the main workload: all | none | comma list of c4_1080p,c5")
     ap.add_argument("--graph", default="auto", choices=["auto", "off"],
                     help="auto: `value` from CUDA-graph replays of the step when capture works")
     args = ap.parse_args()
@@ -626,14 +932,19 @@ def main():
     if args.impl == "reference":
         run_reference(args)
         return
+    wl0 = WORKLOADS[args.workload]
+    if wl0.get("passes") or wl0.get("Tmax"):
+        return main_block(args)
 
     # stdout carries the one JSON line only: whatever libraries print on fd 1 meanwhile (NCCL's version line at N>1)
     # is sent to stderr, and fd 1 comes back for the final print
     sys.stdout.flush()
     real_stdout = os.dup(1)
     os.dup2(2, 1)
+    extra = {}
     try:
         r = run_product(args)
+        extra = run_extras(args, r)
     finally:
         sys.stdout.flush()
         os.dup2(real_stdout, 1)
@@ -655,24 +966,43 @@ def main():
     main_k = [n for n in kt if n in ("search_forward", "search_backward", "wpsum_forward", "wpsum_backward")]
     dom = max(main_k, key=lambda n: kt[n]["ms_total"])
     peak, peak_src = load_peaks()
-    dur_s = kt[dom]["ms_per_launch"] * 1e-3
-    achieved = alg[dom]["bytes"] / dur_s / 1e9
-    roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak,
-                "traffic": load_traffic(args.workload, dom) if world == 1 else None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg[dom]["bytes"], "ms_per_launch": kt[dom]["ms_per_launch"],
-                "share_of_step": kt[dom]["ms_per_step"] / ms_per_step}
     clocks = r["clocks"]
     mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965
-    fma_peak = 148 * 128 * 2 * mhz * 1e6 / 1e12
+    fma_meas = (extra.get("fp32_fma_peak") or {}).get("tflops")
+    fma_peak = fma_meas or 148 * 128 * 2 * mhz * 1e6 / 1e12
+    fma_src = ("measured in this run: stnls_ffma_peak microbenchmark (csrc/peak.cu), CUDA events" if fma_meas else
+               f"formula 148 SM x 128 lanes x 2 x {mhz} MHz (microbenchmark not run)")
+    dur_s = kt[dom]["ms_per_launch"] * 1e-3
+    hbm_ach = alg[dom]["bytes"] / dur_s / 1e9
+    traffic = load_traffic(args.workload, dom) if world == 1 else None
+    roofline = {"kernel": dom, "traffic": traffic,
+                "traffic_source": "profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the "
+                                  "committed `ncu --set full` capture of this kernel (not re-measured in this run)",
+                "algorithmic_bytes_per_launch": alg[dom]["bytes"], "ms_per_launch": kt[dom]["ms_per_launch"],
+                "share_of_step": kt[dom]["ms_per_step"] / ms_per_step,
+                "hbm": {"achieved": hbm_ach, "peak": peak, "unit": "GB/s", "frac": hbm_ach / peak, "peak_source": peak_src}}
+    if dom == "search_forward":
+        # the search forward is bound by the fp32 FMA / issue pipes (arithmetic intensity >> machine balance), not by HBM
+        exe = alg[dom]["flops_executed"] / dur_s / 1e12
+        roofline.update({"bound": "fp32_fma", "achieved": exe, "peak": fma_peak, "unit": "TFLOP/s", "frac": exe / fma_peak,
+                         "peak_source": fma_src,
+                         "flops": "executed: 4 per interpolated lattice point + 2 (prod) / 3 (l2) per patch element"})
+    else:
+        roofline.update({"bound": "hbm", "achieved": hbm_ach, "peak": peak, "unit": "GB/s", "frac": hbm_ach / peak,
+                         "peak_source": peak_src,
+                         "note": "scatter kernel: its limiter is the L2 atomic (RED) rate, DRAM traffic == algorithmic"})
     fwd = kt.get("search_forward")
     roofline_fma = None
     if fwd:
         af = alg["search_forward"]["flops"] / (fwd["ms_per_launch"] * 1e-3) / 1e12
+        ae = alg["search_forward"]["flops_executed"] / (fwd["ms_per_launch"] * 1e-3) / 1e12
         roofline_fma = {"kernel": "search_forward", "bound": "fp32 fma pipe", "achieved": af, "peak": fma_peak,
-                        "unit": "TFLOP/s", "frac": af / fma_peak,
-                        "peak_source": f"148 SM x 128 lanes x 2 x {mhz} MHz (median SM clock under load)",
-                        "algorithmic_flops_per_launch": alg["search_forward"]["flops"]}
+                        "unit": "TFLOP/s", "frac": af / fma_peak, "peak_source": fma_src,
+                        "algorithmic_flops_per_launch": alg["search_forward"]["flops"],
+                        "note": "SURVEY.md 8d flop count (8 flops of bilinear work per patch element of every candidate); "
+                                "the kernel interpolates each lattice point once, so `executed` is the pipe's real load",
+                        "executed": {"achieved": ae, "frac": ae / fma_peak,
+                                     "flops_per_launch": alg["search_forward"]["flops_executed"]}}
     for n in kt:
         if n in alg and alg[n]["bytes"]:
             kt[n]["alg_GBs"] = alg[n]["bytes"] / (kt[n]["ms_per_launch"] * 1e-3) / 1e9
@@ -684,6 +1014,8 @@ def main():
             "frames_per_s": wl["B"] * wl["T"] * world / (ms_per_step * 1e-3),
             "e2e": {"value": e2e_val, "unit": "Gcandidates/s", "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"], "ms_per_step": e2e_ms,
+                    "host_link_GBs_per_rank": {"h2d": r.get("h2d_gbs"), "d2h": r.get("d2h_gbs"),
+                                               "how": "one timed pinned<->device copy of a step's tensors, all ranks at once"},
                     "latency_ms_per_step": r["lat_ms"] / steps,
                     "through": "stnls_b200.parallel.GraphedStep (two buffer slots, one CUDA graph of the step each)"
                                if r["e2e_from"] == "graph" else "eager Python front end",
@@ -709,6 +1041,7 @@ def main():
         line["cpu_baseline"] = {"value": c / t / 1e9, "unit": "Gcandidates/s", "cores": cores, "kind": "port",
                                 "sample": f"{n} pass(es) of the same pipeline on a {crop}x{crop} crop (T={wl['T']}), "
                                           f"oracle/stnls_oracle.c with OpenMP, {t:.1f} s of CPU work"}
+    line.update(extra)
     if world > 1:
         line["config"]["host_affinity"] = (f"rank threads bound to the {r['numa']} CPUs NVML lists for their GPU" if r["numa"]
                                            else "not bound (NVML affinity unavailable)")

@@ -184,8 +184,13 @@ int stnls_anchor_self_time(float* dists, void* inds, const void* flows, int B, i
  * (lib/csrc/agg/gather_add_kernel.cu:94-97).  Returns the minimum count (0 => reference asserts). */
 int stnls_overlap_counts(int* counts, int H, int nH, int ps, int stride0, int dilation, int patch_offset);
 
-/* ---- halo add: dst[i] += src[i]  (multi-GPU gradient halo reduce) ---------------------------- */
+/* ---- halo add: dst[i] += src[i]  (multi-GPU gradient halo reduce); any alignment ------------ */
 int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t stream);
+
+/* ---- measurement aid: fp32 FMA-pipe microbenchmark (no reference counterpart) -------------------
+ * `blocks` CTAs of 256 threads, each thread 16 independent FFMA chains of `iters` steps; flops per launch =
+ * 2*16*iters*256*blocks.  bench.py times it with CUDA events for the fp32 roofline denominator. */
+int stnls_ffma_peak(float* sink, int blocks, int iters, stnls_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -7,7 +7,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB = os.path.join(_HERE, "libstnls_b200.so")
 SOURCES = ["errors.cu", "layout.cu", "search_fwd.cu", "search_fwd_tab_nls_int.cu", "search_fwd_tab_nls_float.cu",
-           "search_fwd_tab_ref_int.cu", "search_fwd_tab_ref_float.cu", "search_fwd_tile_host.cu", "search_fwd_tile_prod.cu", "search_fwd_tile_l2.cu", "search_bwd.cu", "wpsum.cu", "search_flow.cu", "normz.cu", "anchor.cu"]
+           "search_fwd_tab_ref_int.cu", "search_fwd_tab_ref_float.cu", "search_fwd_tile_host.cu", "search_fwd_tile_prod.cu", "search_fwd_tile_l2.cu", "search_bwd.cu", "wpsum.cu", "search_flow.cu", "normz.cu", "anchor.cu", "peak.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

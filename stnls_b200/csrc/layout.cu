@@ -15,6 +15,7 @@ struct LayoutParams {
   const int* counts_h;
   const int* counts_w;
   int accumulate;
+  int64_t nz;   // B*HD*Tloc slabs
 };
 
 // grid (ceil(W/32), H, N*Tloc), block 256, dynamic smem Fp*33 floats
@@ -23,7 +24,8 @@ __global__ void __launch_bounds__(256) layout_kernel(const __grid_constant__ Lay
   extern __shared__ float tile[];  // [Fp][33]
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int w0 = blockIdx.x * 32, h = blockIdx.y;
-  const int tl = blockIdx.z % P.Tloc, n = blockIdx.z / P.Tloc;
+  for (int64_t z = blockIdx.z; z < P.nz; z += gridDim.z) {   // slabs beyond the 65535 a grid's z extent can hold
+  const int tl = (int)(z % P.Tloc), n = (int)(z / P.Tloc);
   const int b = n / P.HD, hd = n % P.HD;
   float* pl = P.planar + (int64_t)b * P.sB + (int64_t)hd * P.sHD + (int64_t)(P.t0 + tl) * P.sT + (int64_t)h * P.W;
   float* cl = P.cl + ((((int64_t)n * P.Tloc + tl) * P.H + h) * P.W + w0) * P.Fp;
@@ -59,6 +61,8 @@ __global__ void __launch_bounds__(256) layout_kernel(const __grid_constant__ Lay
       }
     }
   }
+  __syncthreads();   // the tile is reused by the next slab
+  }
 }
 
 __global__ void add_inplace_kernel(float* dst, const float* src, int64_t n) {
@@ -73,16 +77,26 @@ __global__ void add_inplace_kernel(float* dst, const float* src, int64_t n) {
   }
 }
 
+__global__ void add_inplace_scalar_kernel(float* dst, const float* src, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] += src[i];
+}
+
 int launch_layout(bool pack, LayoutParams& P, int B, cudaStream_t st, const char* who) {
   STNLS_REQUIRE(P.cl && P.planar, "%s: null argument", who);
   STNLS_REQUIRE(P.Fp % 4 == 0 && P.Fp >= P.F && P.F > 0, "%s: Fp must be a multiple of 4 and >= F", who);
   STNLS_REQUIRE(P.H <= 65535, "%s: H too large", who);
   int64_t nz = (int64_t)B * P.HD * P.Tloc;
   if (nz == 0 || P.H == 0 || P.W == 0) return STNLS_OK;
-  STNLS_REQUIRE(nz <= 65535, "%s: B*HD*T too large for one launch", who);
-  dim3 grid((P.W + 31) / 32, P.H, (unsigned)nz);
+  P.nz = nz;
+  dim3 grid((P.W + 31) / 32, P.H, (unsigned)(nz < 65535 ? nz : 65535));
   size_t smem = (size_t)P.Fp * 33 * sizeof(float);
-  STNLS_REQUIRE(smem <= 48 * 1024, "%s: too many channels per head (%d)", who, P.F);
+  STNLS_REQUIRE(smem <= 227 * 1024, "%s: too many channels per head (%d)", who, P.F);
+  if (smem > 48 * 1024) {   // more than 372 channels per head: opt in to the large carve-out
+    cudaError_t e = pack ? cudaFuncSetAttribute(layout_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                         : cudaFuncSetAttribute(layout_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    STNLS_REQUIRE(e == cudaSuccess, "%s: cannot reserve %zu bytes of shared memory", who, smem);
+  }
   if (pack) layout_kernel<true><<<grid, 256, smem, st>>>(P);
   else layout_kernel<false><<<grid, 256, smem, st>>>(P);
   STNLS_CHECK_LAUNCH(who);
@@ -115,9 +129,13 @@ extern "C" int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, i
 extern "C" int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t stream) {
   STNLS_REQUIRE(dst && src, "add_inplace: null argument");
   if (n <= 0) return STNLS_OK;
-  int64_t nthr = (n + 3) / 4;
+  // the vector kernel needs 16-byte aligned operands (a frame slice of an odd-sized video is not): scalar otherwise
+  const bool aligned = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0;
+  int64_t nthr = aligned ? (n + 3) / 4 : n;
+  STNLS_REQUIRE((nthr + 255) / 256 < 2147483647LL, "add_inplace: too many elements for one launch");
   unsigned blocks = (unsigned)((nthr + 255) / 256);
-  add_inplace_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dst, src, n);
+  if (aligned) add_inplace_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dst, src, n);
+  else add_inplace_scalar_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dst, src, n);
   STNLS_CHECK_LAUNCH("add_inplace");
   return STNLS_OK;
 }

@@ -156,7 +156,6 @@ extern "C" int stnls_search_forward(const float* q_cl, const float* k_cl, const 
   STNLS_REQUIRE(o->dist_type == 0 || o->dist_type == 1, "Uknown distance type. Must be 0 (product) or 1 (l2)");
   STNLS_REQUIRE(o->ps > 0, "search_forward: patch size is invalid [%d]", o->ps);
   const bool refine = o->wr > 0;
-  if (int rc = stnls_check_geom(g, refine ? -1 : o->wt, "search_forward")) return rc;
   FwdParams P;
   P.q = q_cl; P.k = k_cl; P.flows = flows; P.dists = dists; P.inds = inds; P.kselect = kselect; P.reflect = reflect;
   P.g = *g; P.o = *o;
@@ -170,6 +169,7 @@ extern "C" int stnls_search_forward(const float* q_cl, const float* k_cl, const 
     STNLS_REQUIRE(o->st_offset == 0 || o->st_offset == 1, "search_forward: flows.size(3) must be W_t or W_t-1");
     P.G = o->ws * o->ws; P.nG = P.W_t; P.wsz = o->ws;
   }
+  if (int rc = stnls_check_geom(g, refine ? -1 : o->wt, "search_forward")) return rc;
   P.L = P.G * P.nG;
   P.Kout = (o->K > 0) ? (o->K < P.L ? o->K : P.L) : P.L;
   STNLS_REQUIRE(o->K <= 0 || P.Kout <= 32 + (o->anchor_self ? 1 : 0),

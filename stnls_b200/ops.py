@@ -277,3 +277,22 @@ def add_inplace(dst, src):
     assert dst.is_contiguous() and src.is_contiguous() and dst.numel() == src.numel()
     _launch("add_inplace", _C.lib().stnls_add_inplace, _ptr(dst), _ptr(src), dst.numel(), _stream())
     return dst
+
+
+def ffma_peak_tflops(device, iters=4096, reps=5):
+    """Measured fp32 FMA-pipe throughput of `device` in TFLOP/s (stnls_ffma_peak, CUDA events, best of `reps`)."""
+    sms = th.cuda.get_device_properties(device).multi_processor_count
+    blocks = sms * 8
+    sink = th.zeros(4, device=device)
+    flops = 2.0 * 16 * iters * 256 * blocks
+    best = None
+    for i in range(reps + 2):
+        e0, e1 = th.cuda.Event(enable_timing=True), th.cuda.Event(enable_timing=True)
+        e0.record()
+        _C.check(_C.lib().stnls_ffma_peak(_ptr(sink), blocks, iters, _stream()))
+        e1.record()
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        if i >= 2:
+            best = ms if best is None else min(best, ms)
+    return flops / (best * 1e-3) / 1e12

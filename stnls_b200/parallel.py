@@ -79,6 +79,39 @@ class ShardPlan:
         return sum(hi - lo for _, lo, hi in self.recvs()) * frame_bytes
 
 
+def flat_shard(B, T, wt, world, rank):
+    """Shard the flattened (B, T) frame axis contiguously over `world` ranks, never finer than a frame and never across
+    a batch element (batch elements are independent: lib/csrc/search/non_local_search_int_kernel.cu:55-56).
+    world >= B: world/B ranks share one batch element (C4: B=2, T=32, 8 ranks -> ranks 0-3 own batch 0, 4-7 batch 1),
+    the halo exchange runs inside that sub-group.  world < B: every rank takes B/world whole clips, no halo.
+    Returns (batch slice, ShardPlan inside the sub-group, ranks of the sub-group)."""
+    if world >= B:
+        if world % B:
+            raise ValueError(f"world size {world} must be a multiple of the batch size {B}")
+        rpb = world // B
+        b, local = divmod(rank, rpb)
+        return slice(b, b + 1), ShardPlan(T, wt, rpb, local), list(range(b * rpb, (b + 1) * rpb))
+    if B % world:
+        raise ValueError(f"batch size {B} must be a multiple of the world size {world}")
+    per = B // world
+    return slice(rank * per, (rank + 1) * per), ShardPlan(T, wt, 1, 0), [rank]
+
+
+def batch_groups(B, world, rank, backend=None):
+    """One process group per batch element (see flat_shard); every rank creates all of them, in the same order, as
+    torch.distributed requires.  Returns this rank's group (None when it works alone)."""
+    if world <= B or world // B == 1:
+        return None
+    rpb = world // B
+    mine = None
+    for b in range(B):
+        ranks = list(range(b * rpb, (b + 1) * rpb))
+        grp = dist.new_group(ranks, backend=backend)
+        if rank in ranks:
+            mine = grp
+    return mine
+
+
 def _run_p2p(ops_list):
     if ops_list:
         for w in dist.batch_isend_irecv(ops_list):
@@ -87,6 +120,11 @@ def _run_p2p(ops_list):
 
 def _time_dim(x):
     return 1 if x.dim() == 5 else 2  # (B,T,F,H,W) or (B,HD,T,F,H,W)
+
+
+def _peer(group, local_rank):
+    """global rank of `local_rank` of `group` (send/recv take global ranks)"""
+    return local_rank if group is None else dist.get_global_rank(group, local_rank)
 
 
 def _exchange_forward(x, plan, group):
@@ -98,13 +136,13 @@ def _exchange_forward(x, plan, group):
     p2p, stage = [], []
     for dst, lo, hi in plan.sends():
         buf = x.narrow(td, lo - plan.a, hi - lo).contiguous()
-        p2p.append(dist.P2POp(dist.isend, buf, dst, group))
+        p2p.append(dist.P2POp(dist.isend, buf, _peer(group, dst), group))
     for src, lo, hi in plan.recvs():
         s = list(x.shape)
         s[td] = hi - lo
         buf = x.new_empty(s)
         stage.append((buf, lo, hi))
-        p2p.append(dist.P2POp(dist.irecv, buf, src, group))
+        p2p.append(dist.P2POp(dist.irecv, buf, _peer(group, src), group))
     _run_p2p(p2p)
     for buf, lo, hi in stage:
         ext.narrow(td, lo - plan.fa, hi - lo).copy_(buf)
@@ -118,13 +156,13 @@ def _exchange_backward(gext, plan, group):
     p2p, stage = [], []
     for src, lo, hi in plan.recvs():      # frames we borrowed -> give their gradient back
         buf = gext.narrow(td, lo - plan.fa, hi - lo).contiguous()
-        p2p.append(dist.P2POp(dist.isend, buf, src, group))
+        p2p.append(dist.P2POp(dist.isend, buf, _peer(group, src), group))
     for dst, lo, hi in plan.sends():      # frames we lent -> receive their gradient
         s = list(gown.shape)
         s[td] = hi - lo
         buf = gown.new_empty(s)
         stage.append((buf, lo, hi))
-        p2p.append(dist.P2POp(dist.irecv, buf, dst, group))
+        p2p.append(dist.P2POp(dist.irecv, buf, _peer(group, dst), group))
     _run_p2p(p2p)
     for buf, lo, hi in stage:
         tgt = gown.narrow(td, lo - plan.a, hi - lo)
@@ -255,25 +293,70 @@ class ShardedSearchAgg(th.nn.Module):
         self.peer = None
         self.halo_kind = "none" if plan.world == 1 else "nccl"
         if plan.world > 1 and halo in ("peer", "auto") and th.cuda.is_available() and dist.get_backend() == "nccl":
+            err = None
             try:
                 self.peer = PeerHalo(plan, group)
+            except Exception as exc:   # symmetric memory not available on this box / for this group
+                err = exc
+            # every rank of the group must take the same path: a rank whose rendezvous failed drags the others to NCCL
+            ok = th.tensor([0.0 if self.peer is None else 1.0], device="cuda")
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if float(ok[0]) > 0.5:
                 self.halo_kind = "peer"
-            except Exception:
+            else:
+                self.peer = None
                 if halo == "peer":
-                    raise
+                    raise RuntimeError(f"peer-memory halo exchange unavailable on some rank: {err}")
 
     def forward(self, q, k, v, flows, v_ready=None):
         """v_ready: optional CUDA event after which `v` is valid (e.g. its host->device copy on a side stream);
         the current stream waits for it only when the aggregation needs v, so the copy overlaps the search."""
         k_ext = halo_exchange(k, self.plan, self.group, self.peer, "k")
+        assert k_ext.shape[_time_dim(k_ext)] == self.plan.fb - self.plan.fa, "k must hold the owned frames + halo"
         dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
         sign = -1.0 if self.search.dist_type == "l2" else 1.0
         weights = softmax_scaled(dists, sign * self.scale)   # fused sign/scale/softmax (normz, SURVEY.md 8f N2)
         if v_ready is not None:
             th.cuda.current_stream().wait_event(v_ready)
         v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
+        assert v_ext.shape[_time_dim(v_ext)] == self.plan.fb - self.plan.fa, "v must hold the owned frames + halo"
         out = self.agg(v_ext, weights, inds, shard=self.plan.shard)
         return out, dists, inds
+
+    def chunked_step(self, q, k, v, flows, gout, frames_per_chunk, flows_grad=True):
+        """Forward + backward of sum(out * gout) over the owned frames in chunks of `frames_per_chunk` frames, so that
+        the intermediates of only one chunk are alive at a time (a 1080p rank holds 16 GB of indices per 8 frames).
+        ONE halo exchange per tensor and direction, as in forward(): the exchanged k / v are cut from the graph, every
+        chunk runs search -> softmax -> aggregation -> backward on its frames with shard=(T, tq0, tk0) of its own
+        window, the halo gradients accumulate in place and travel back once.  Returns (out, grad_q, grad_k, grad_v,
+        grad_flows) for the owned frames."""
+        plan = self.plan
+        q, k, v = (x.detach().requires_grad_(True) for x in (q, k, v))
+        flows = flows.detach().requires_grad_(flows_grad and flows.is_floating_point())
+        k_ext = halo_exchange(k, plan, self.group, self.peer, "k")
+        v_ext = halo_exchange(v, plan, self.group, self.peer, "v")
+        kx, vx = k_ext.detach().requires_grad_(True), v_ext.detach().requires_grad_(True)
+        sign = -1.0 if self.search.dist_type == "l2" else 1.0
+        td = _time_dim(q)
+        outs = []
+        for a in range(plan.a, plan.b, frames_per_chunk):
+            b = min(a + frames_per_chunk, plan.b)
+            fa, fb = needed_frames(a, b, plan.T, plan.wt)
+            sh = dict(T=plan.T, tq0=a, tk0=fa)
+            qc = q.narrow(td, a - plan.a, b - a)
+            fc = flows.narrow(2, a - plan.a, b - a)
+            dists, inds = self.search(qc, kx.narrow(td, fa - plan.fa, fb - fa), fc, shard=sh)
+            weights = softmax_scaled(dists, sign * self.scale)
+            out = self.agg(vx.narrow(td, fa - plan.fa, fb - fa), weights, inds, shard=sh)
+            (out * gout.narrow(2, a - plan.a, b - a)).sum().backward()
+            outs.append(out.detach())
+            del dists, inds, weights, out
+        if plan.world > 1:
+            th.autograd.backward([k_ext, v_ext], [kx.grad, vx.grad])
+            gk, gv = k.grad, v.grad
+        else:
+            gk, gv = kx.grad, vx.grad
+        return th.cat(outs, 2), q.grad, gk, gv, flows.grad
 
 
 class GraphedStep:

@@ -3,7 +3,8 @@
 usage: python tools/ncu_summary.py out.json rep1.ncu-rep [rep2 ...]"""
 import csv, json, subprocess, sys
 
-KEEP = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "sm__cycles_elapsed.max",
+KEEP = ["gpu__time_duration.sum", "gpc__cycles_elapsed.avg.per_second", "dram__cycles_elapsed.avg.per_second",
+        "smsp__cycles_elapsed.avg.per_second", "dram__bytes_read.sum", "dram__bytes_write.sum", "sm__cycles_elapsed.max",
         "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",

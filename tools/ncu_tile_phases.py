@@ -22,13 +22,14 @@ def find(pat, start=0):
     for i in range(start, len(src)):
         if pat in src[i]: return i + 1
     raise SystemExit("marker not found: " + pat)
-marks = [("core", find("__device__ __forceinline__ float acc1"), find("// rows of finished candidates handed over per flush")),
-         ("prologue", find("// ---- which tile ----"), find("// K best of a query's pool")),
-         ("merge", find("// K best of a query's pool"), find("for (int st = 0; st < W_t; st++) {", find("// K best of a query's pool"))),
-         ("frame_head(wait,mirror)", find("for (int st = 0; st < W_t; st++) {", find("// K best of a query's pool")), find("// pool slot of this frame slot's candidate 0")),
-         ("qload", find("// query patch, this lane's channel"), find("// one integer-spaced (sub-)window")),
-         ("flush", find("auto flush = [&]"), find("tile_core<WH, WW, PS, DIST, FP, G>(bp")),
-         ("output", find("// ---- outputs: the sorted list"), find("// ---- queries this tile could not stage"))]
+loop = find("for (int st = 0; st < W_t; st++) {", find("// ---- frame slots: TMA box"))
+marks = [("core (interpolate + accumulate)", find("__device__ __forceinline__ float acc1"), find("// ---- pool compaction")),
+         ("tile_merge (pool compaction)", find("// ---- pool compaction"), find("// rows of finished candidates handed over per flush")),
+         ("prologue (geometry, q tile, TMA issue)", find("// ---- which tile ----"), loop),
+         ("frame head (mbarrier wait, mirror fill)", loop, find("for (int pass = 0;", loop)),
+         ("q patch load", find("// query patch, this lane's channel"), find("// one integer-spaced (sub-)window")),
+         ("flush (transpose-sum, key, append)", find("auto flush = [&]"), find("tile_core<WH, WW, PS, DIST, FP, G>(bp")),
+         ("output (final compaction call, dists/inds)", find("// ---- outputs: the sorted list"), find("// ---- queries this tile could not stage"))]
 rep = sys.argv[1]; units = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
 L = lines(rep)
 tot = sum(x[2] for x in L); ts = sum(x[3] for x in L)
