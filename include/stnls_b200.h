@@ -187,6 +187,12 @@ int stnls_overlap_counts(int* counts, int H, int nH, int ps, int stride0, int di
 /* ---- halo add: dst[i] += src[i]  (multi-GPU gradient halo reduce); any alignment ------------ */
 int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t stream);
 
+/* ---- halo staging / pull: up to 8 contiguous segments copied (accumulate == 0) or added with vector REDs
+ * (accumulate != 0) in one launch; dst[i], src[i] 16-byte aligned, nfloat[i] a multiple of 4.  src may be memory of a
+ * peer GPU mapped into this process (NVLink peer loads).  The arrays are HOST arrays of nseg entries.          */
+int stnls_seg_copy(float* const* dst, const float* const* src, const int64_t* nfloat, int nseg, int accumulate,
+                   stnls_stream_t stream);
+
 /* ---- measurement aid: fp32 FMA-pipe microbenchmark (no reference counterpart) -------------------
  * `blocks` CTAs of 256 threads, each thread 16 independent FFMA chains of `iters` steps; flops per launch =
  * 2*16*iters*256*blocks.  bench.py times it with CUDA events for the fp32 roofline denominator. */

@@ -37,7 +37,7 @@ EXPORTS = ["stnls_last_error", "stnls_version", "stnls_pack_cl", "stnls_unpack_c
            "stnls_wpsum_backward", "stnls_gather_forward", "stnls_gather_backward",
            "stnls_search_flow_forward", "stnls_search_flow_backward",
            "stnls_softmax_forward", "stnls_softmax_backward", "stnls_anchor_self_time",
-           "stnls_overlap_counts", "stnls_add_inplace", "stnls_ffma_peak"]
+           "stnls_overlap_counts", "stnls_add_inplace", "stnls_ffma_peak", "stnls_seg_copy"]
 
 _lib = None
 
@@ -74,6 +74,7 @@ def lib():
     L.stnls_overlap_counts.argtypes = [c_vp] + [c_int] * 6
     L.stnls_add_inplace.argtypes = [c_vp, c_vp, c_i64, c_vp]
     L.stnls_ffma_peak.argtypes = [c_vp, c_int, c_int, c_vp]
+    L.stnls_seg_copy.argtypes = [c_vp, c_vp, c_vp, c_int, c_int, c_vp]
     for name in EXPORTS:
         getattr(L, name)  # raises AttributeError if a declared symbol is missing
     _lib = L

@@ -82,6 +82,27 @@ __global__ void add_inplace_scalar_kernel(float* dst, const float* src, int64_t 
   if (i < n) dst[i] += src[i];
 }
 
+// up to 8 contiguous segment copies (or accumulations) in ONE launch: the halo exchange stages / pulls the frames of
+// several tensors and several neighbours at once (stnls_b200/parallel.py PeerHalo).  Sources may be peer-GPU pointers.
+struct SegJobs {
+  float* dst[8];
+  const float* src[8];
+  int64_t n4[8];      // float4 elements (segments are 16-byte multiples, 16-byte aligned)
+  int nseg, accumulate;
+};
+__global__ void __launch_bounds__(256) seg_copy_kernel(const __grid_constant__ SegJobs J) {
+  const int sgm = blockIdx.y;
+  const float4* src = reinterpret_cast<const float4*>(J.src[sgm]);
+  float* dst = J.dst[sgm];
+  const int64_t n4 = J.n4[sgm];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = src[i];
+    // accumulate: two neighbours may return gradient for the same frame -> vector RED, not a read-modify-write
+    if (J.accumulate) red_add4(dst + i * 4, v);
+    else reinterpret_cast<float4*>(dst)[i] = v;
+  }
+}
+
 int launch_layout(bool pack, LayoutParams& P, int B, cudaStream_t st, const char* who) {
   STNLS_REQUIRE(P.cl && P.planar, "%s: null argument", who);
   STNLS_REQUIRE(P.Fp % 4 == 0 && P.Fp >= P.F && P.F > 0, "%s: Fp must be a multiple of 4 and >= F", who);
@@ -137,5 +158,28 @@ extern "C" int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_
   if (aligned) add_inplace_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dst, src, n);
   else add_inplace_scalar_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dst, src, n);
   STNLS_CHECK_LAUNCH("add_inplace");
+  return STNLS_OK;
+}
+
+extern "C" int stnls_seg_copy(float* const* dst, const float* const* src, const int64_t* nfloat, int nseg, int accumulate,
+                              stnls_stream_t stream) {
+  STNLS_REQUIRE(dst && src && nfloat && nseg >= 0 && nseg <= 8, "seg_copy: 0..8 segments");
+  if (nseg == 0) return STNLS_OK;
+  SegJobs J;
+  int64_t most = 0;
+  for (int i = 0; i < nseg; i++) {
+    STNLS_REQUIRE(dst[i] && src[i] && nfloat[i] >= 0 && nfloat[i] % 4 == 0, "seg_copy: segment %d: null or not a multiple of 4 floats", i);
+    STNLS_REQUIRE(((reinterpret_cast<uintptr_t>(dst[i]) | reinterpret_cast<uintptr_t>(src[i])) & 15) == 0,
+                  "seg_copy: segment %d is not 16-byte aligned", i);
+    J.dst[i] = dst[i]; J.src[i] = src[i]; J.n4[i] = nfloat[i] / 4;
+    most = J.n4[i] > most ? J.n4[i] : most;
+  }
+  J.nseg = nseg; J.accumulate = accumulate;
+  if (most == 0) return STNLS_OK;
+  int64_t bx = (most + 256 * 8 - 1) / (256 * 8);
+  if (bx > 148 * 16) bx = 148 * 16;
+  if (bx < 1) bx = 1;
+  seg_copy_kernel<<<dim3((unsigned)bx, (unsigned)nseg), 256, 0, (cudaStream_t)stream>>>(J);
+  STNLS_CHECK_LAUNCH("seg_copy");
   return STNLS_OK;
 }

@@ -34,7 +34,7 @@ struct BwdParams {
   const uint8_t* reflect;
   stnls_geom g;
   stnls_search_opts o;
-  int K, mode, nquad, W_t, fast3, ksplit;
+  int K, mode, nquad, W_t, fast3, ksplit, qagg;
   int64_t nthreads;
 };
 
@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
   const int rw = (MODE == 0) ? (nw * o.strideQ) % g.qW : aw;
   const int hd_f = hd % o.HD_f;
   const int ps = (PS > 0) ? PS : o.ps;
+  const unsigned qmask = P.qagg ? ((P.nquad >= 32 ? 0xffffffffu : ((1u << P.nquad) - 1u)) << ((threadIdx.x & 31) & ~(P.nquad - 1))) : 0u;
 
   const float* qf = P.q + ((int64_t)n * g.Tq + tl) * g.qH * g.qW * g.Fp + c4;
   float* gqf = P.gq + ((int64_t)n * g.Tq + tl) * g.qH * g.qW * g.Fp + c4;
@@ -154,6 +155,13 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
     };
     // flow-gradient tail of one neighbour (non_local_search_bilin2d_kernel.cu:555-594 ; shared_kernel.cu:1001-1026)
     auto tail = [&](const Pre& z, float dfw, float dfh) {
+      if (MODE >= 2 && P.qagg) {   // one pair of atomics per (query, neighbour): sum the channel-quad lanes first
+        for (int off = P.nquad >> 1; off > 0; off >>= 1) {
+          dfw += __shfl_xor_sync(qmask, dfw, off);
+          dfh += __shfl_xor_sync(qmask, dfh, off);
+        }
+        if (c4 != 0) return;
+      }
       if (MODE == 2) {
         const int dt = (int)z.pp0 - t;
         const int dto = time_tmax(t, g.T, o.wt) - t;
@@ -373,6 +381,7 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   if (P.mode == 2) STNLS_REQUIRE(flows != nullptr, "search_backward: flows required with grad_flows");
   if (P.mode == 3) STNLS_REQUIRE(kselect && reflect, "search_backward: kselect/reflect required for refine flow grads");
   P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->nH * g->nW * P.nquad;
+  P.qagg = (P.nquad > 1 && P.nquad <= 32 && (P.nquad & (P.nquad - 1)) == 0 && !getenv("STNLS_NO_QAGG")) ? 1 : 0;
   if (P.nthreads == 0 || K == 0) return STNLS_OK;
   // float modes, small launches: one thread per (query, neighbour, quad)
   // measured on B200 (profiles/README.md): with ps=3 the split form wins while the whole problem is a few

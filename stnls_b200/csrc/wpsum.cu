@@ -29,6 +29,7 @@ struct AggParams {
   stnls_agg_opts o;
   int nquad;
   int stack;         // 1: NonLocalGather -- no sum over K, slab (n*K + k) of out / gout belongs to neighbour k
+  int qagg;          // backward: channel quads are a power of two -> per-pair sums are reduced across the quad lanes
   int64_t nthreads;
 };
 
@@ -271,6 +272,15 @@ __global__ void __launch_bounds__(512) wpsum_fwd_tile_kernel(const __grid_consta
 }
 
 
+// Sum over the channel-quad lanes of one (query, neighbour): the `nq` lanes (a power of two <= 32, adjacent, all on the
+// same control path because every branch above depends on (query, neighbour) only) hold partial dot products; after
+// the butterfly lane c4 == 0 issues the ONE store / atomic of the pair -- the reference issues ps*ps atomics per pair
+// and channel (gather_add_kernel.cu:315), the round-1 kernel one per channel quad.
+__device__ __forceinline__ float quad_sum(float v, int nq, unsigned mask) {
+  for (int off = nq >> 1; off > 0; off >>= 1) v += __shfl_xor_sync(mask, v, off);
+  return v;
+}
+
 // FAST3: ps == 3 && dilation == 1.  The 9 bilinear reads of one neighbour patch then share a 4x4
 // pixel footprint (all patch pixels have the same fractional position), so an interior (query, k)
 // pair reads 16 value pixels and issues 16 vector REDs instead of 36 + 36.
@@ -297,6 +307,7 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
   const int64_t vfs = (int64_t)H * W * g.Fp;
   const float* vb = P.v + (int64_t)n * g.Tk * vfs + c4;
   float* gvb = P.out + (int64_t)n * g.Tk * vfs + c4;
+  const unsigned qmask = P.qagg ? ((P.nquad >= 32 ? 0xffffffffu : ((1u << P.nquad) - 1u)) << ((threadIdx.x & 31) & ~(P.nquad - 1))) : 0u;
   const float* gof = P.gout + ((P.stack ? (int64_t)n * o.K + k_lo : (int64_t)n) * g.Tq + tl) * vfs + c4;  // stack => KSPLIT
 
   // generic path for one neighbour: every patch pixel validated / reflected on its own
@@ -389,6 +400,11 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
         }
       }
     }
+    if (P.qagg) {   // one atomic per (query, neighbour): sum the channel-quad lanes first
+      accw = quad_sum(accw, P.nquad, qmask);
+      if (!INT) { fh = quad_sum(fh, P.nquad, qmask); fw = quad_sum(fw, P.nquad, qmask); }
+      if (c4 != 0) return;
+    }
     atomicAdd(P.gweights + oi, accw);
     if (!INT) {
       atomicAdd(P.gflows + oi * 3 + 1, fh);
@@ -468,6 +484,12 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
     }
 #pragma unroll
     for (int j = 0; j < 4; j++) red_add4(gr_ + 3 * rs + j * g.Fp, accA[j]);
+    if (P.qagg) {
+      accw = quad_sum(accw, P.nquad, qmask);
+      aH = quad_sum(aH, P.nquad, qmask);
+      aW = quad_sum(aW, P.nquad, qmask);
+      if (c4 != 0) continue;
+    }
     atomicAdd(P.gweights + oi, accw);
     atomicAdd(P.gflows + oi * 3 + 1, weight * aH);
     atomicAdd(P.gflows + oi * 3 + 2, weight * aW);
@@ -504,7 +526,7 @@ static int agg_forward(float* out_cl, const float* v_cl, const float* weights, c
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_forward: too many threads for one launch");
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
   cudaStream_t st = (cudaStream_t)stream;
-  if (!stack && o->ps == 3 && o->dilation == 1 && P.nquad <= 4 && !getenv("STNLS_WPF_NO_TILE")) {
+  if (!stack && o->ps == 3 && o->dilation == 1 && P.nquad <= 8 && !getenv("STNLS_WPF_NO_TILE")) {
     // tile: the largest with (queries touching the tile) x quads <= 512 threads
     static const int dims[5][2] = {{16, 32}, {16, 16}, {12, 16}, {8, 16}, {8, 8}};
     TileCfg C = {};
@@ -553,6 +575,7 @@ static int agg_backward(float* gv_cl, float* grad_weights, float* grad_flows, co
   P.out = gv_cl; P.gweights = grad_weights; P.gflows = grad_flows; P.gout = gout_cl; P.v = v_cl;
   P.weights = weights; P.flows = flows; P.g = *g; P.o = *o; P.nquad = g->Fp / 4;
   P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->nH * g->nW * P.nquad;
+  P.qagg = (P.nquad > 1 && P.nquad <= 32 && (P.nquad & (P.nquad - 1)) == 0 && !getenv("STNLS_NO_QAGG")) ? 1 : 0;
   if (P.nthreads == 0 || o->K == 0) return STNLS_OK;
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_backward: too many threads for one launch");
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);

@@ -216,6 +216,26 @@ def gather_backward(gstack_cl, v_cl, weights, flows, geom, opts):
     return gv, gw, gf
 
 
+def seg_copy(pairs, accumulate=False):
+    """[(dst, src)] contiguous fp32 tensors of equal numel (numel % 4 == 0, 16-byte aligned) copied -- or added with
+    vector REDs -- in ONE launch (at most 8 pairs per launch).  src may live on a peer GPU (symmetric memory)."""
+    pairs = [(d, s_) for d, s_ in pairs if d.numel()]
+    for i in range(0, len(pairs), 8):
+        chunk = pairs[i:i + 8]
+        n = len(chunk)
+        for d, s_ in chunk:
+            assert d.is_contiguous() and s_.is_contiguous() and d.numel() == s_.numel() and d.dtype == th.float32
+        dst = (ctypes.c_void_p * n)(*[d.data_ptr() for d, _ in chunk])
+        src = (ctypes.c_void_p * n)(*[s_.data_ptr() for _, s_ in chunk])
+        cnt = (ctypes.c_int64 * n)(*[d.numel() for d, _ in chunk])
+        _launch("seg_copy", _C.lib().stnls_seg_copy, dst, src, cnt, n, int(accumulate), _stream())
+
+
+def seg_copy_ok(*ts):
+    return all(t.is_cuda and t.dtype == th.float32 and t.is_contiguous() and t.numel() % 4 == 0 and t.data_ptr() % 16 == 0
+               for t in ts)
+
+
 def _flow_check(fflow, bflow):
     _need_cuda(fflow, bflow)
     if fflow.dim() != 5 or fflow.shape[2] != 2 or fflow.shape != bflow.shape:

@@ -258,6 +258,75 @@ class PeerHalo:
         return gown
 
 
+    # ---- several tensors per exchange, three launches in all ------------------------------------------------------
+    # stage (one segmented-copy launch) -> ONE barrier -> pull (one segmented-copy launch: own frames + the halo frames
+    # of every tensor from every neighbour, NVLink peer loads).  Backward: stage, barrier, own part, then the lent
+    # slices ADDED with vector REDs (two neighbours may return gradient for the same frame).  Needs the frames of a
+    # tensor to be contiguous in memory: planar (1,T,F,H,W) videos, i.e. one batch element per rank.
+    @staticmethod
+    def fast_ok(xs):
+        from . import ops
+        return all(x.dim() == 5 and x.shape[0] == 1 and ops.seg_copy_ok(x) and x[0, 0].numel() % 4 == 0 for x in xs)
+
+    def forward_multi(self, xs, tag):
+        from . import ops
+        plan = self.plan
+        n_own, n_ext = plan.b - plan.a, plan.fb - plan.fa
+        staged = []
+        for i, x in enumerate(xs):
+            buf, hdl = self._buffers(("f", tag, i), self.max_own, tuple(x.shape[2:]), x.dtype, x.device)
+            staged.append((buf, hdl))
+        ops.seg_copy([(buf[:n_own], x[0]) for (buf, _), x in zip(staged, xs)])
+        staged[0][1].barrier(channel=0)
+        exts, jobs = [], []
+        for (buf, hdl), x in zip(staged, xs):
+            ext = x.new_empty((1, n_ext) + tuple(x.shape[2:]))
+            jobs.append((ext[0, plan.a - plan.fa:plan.b - plan.fa], x[0]))
+            for src, lo, hi in plan.recvs():
+                a_src = plan.owned[src][0]
+                peer = hdl.get_buffer(src, (self.max_own,) + tuple(x.shape[2:]), x.dtype)
+                jobs.append((ext[0, lo - plan.fa:hi - plan.fa], peer[lo - a_src:hi - a_src]))
+            exts.append(ext)
+        ops.seg_copy(jobs)
+        return exts
+
+    def backward_multi(self, gexts, tag):
+        from . import ops
+        plan = self.plan
+        n_own, n_ext = plan.b - plan.a, plan.fb - plan.fa
+        staged = []
+        for i, g in enumerate(gexts):
+            buf, hdl = self._buffers(("b", tag, i), self.max_ext, tuple(g.shape[2:]), g.dtype, g.device)
+            staged.append((buf, hdl))
+        ops.seg_copy([(buf[:n_ext], g[0]) for (buf, _), g in zip(staged, gexts)])
+        staged[0][1].barrier(channel=0)
+        gowns, own_jobs, add_jobs = [], [], []
+        for (buf, hdl), g in zip(staged, gexts):
+            gown = g.new_empty((1, n_own) + tuple(g.shape[2:]))
+            own_jobs.append((gown[0], g[0, plan.a - plan.fa:plan.b - plan.fa]))
+            for dst, lo, hi in plan.sends():          # frames we lent to dst: their gradient sits in dst's buffer
+                fa_dst = plan.need[dst][0]
+                peer = hdl.get_buffer(dst, (self.max_ext,) + tuple(g.shape[2:]), g.dtype)
+                add_jobs.append((gown[0, lo - plan.a:hi - plan.a], peer[lo - fa_dst:hi - fa_dst]))
+            gowns.append(gown)
+        ops.seg_copy(own_jobs)
+        ops.seg_copy(add_jobs, accumulate=True)
+        return gowns
+
+
+class PeerHaloExchangeMulti(th.autograd.Function):
+    """k and v (any number of planar videos) through ONE peer-memory exchange per direction (PeerHalo.forward_multi)."""
+
+    @staticmethod
+    def forward(ctx, peer, tag, *xs):
+        ctx.peer, ctx.tag = peer, tag
+        return tuple(peer.forward_multi([x.contiguous() for x in xs], tag))
+
+    @staticmethod
+    def backward(ctx, *gs):
+        return (None, None) + tuple(ctx.peer.backward_multi([g.contiguous() for g in gs], ctx.tag))
+
+
 class PeerHaloExchange(th.autograd.Function):
     """HaloExchange over peer memory (see PeerHalo)."""
 
@@ -311,14 +380,19 @@ class ShardedSearchAgg(th.nn.Module):
     def forward(self, q, k, v, flows, v_ready=None):
         """v_ready: optional CUDA event after which `v` is valid (e.g. its host->device copy on a side stream);
         the current stream waits for it only when the aggregation needs v, so the copy overlaps the search."""
-        k_ext = halo_exchange(k, self.plan, self.group, self.peer, "k")
+        joint = self.peer is not None and v_ready is None and PeerHalo.fast_ok([k, v])
+        if joint:   # k and v in one exchange: one barrier and two copy launches for both (and for both gradients)
+            k_ext, v_ext = PeerHaloExchangeMulti.apply(self.peer, "kv", k, v)
+        else:
+            k_ext = halo_exchange(k, self.plan, self.group, self.peer, "k")
         assert k_ext.shape[_time_dim(k_ext)] == self.plan.fb - self.plan.fa, "k must hold the owned frames + halo"
         dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
         sign = -1.0 if self.search.dist_type == "l2" else 1.0
         weights = softmax_scaled(dists, sign * self.scale)   # fused sign/scale/softmax (normz, SURVEY.md 8f N2)
         if v_ready is not None:
             th.cuda.current_stream().wait_event(v_ready)
-        v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
+        if not joint:
+            v_ext = halo_exchange(v, self.plan, self.group, self.peer, "v")
         assert v_ext.shape[_time_dim(v_ext)] == self.plan.fb - self.plan.fa, "v must hold the owned frames + halo"
         out = self.agg(v_ext, weights, inds, shard=self.plan.shard)
         return out, dists, inds
@@ -333,8 +407,11 @@ class ShardedSearchAgg(th.nn.Module):
         plan = self.plan
         q, k, v = (x.detach().requires_grad_(True) for x in (q, k, v))
         flows = flows.detach().requires_grad_(flows_grad and flows.is_floating_point())
-        k_ext = halo_exchange(k, plan, self.group, self.peer, "k")
-        v_ext = halo_exchange(v, plan, self.group, self.peer, "v")
+        if self.peer is not None and PeerHalo.fast_ok([k, v]):
+            k_ext, v_ext = PeerHaloExchangeMulti.apply(self.peer, "kv", k, v)
+        else:
+            k_ext = halo_exchange(k, plan, self.group, self.peer, "k")
+            v_ext = halo_exchange(v, plan, self.group, self.peer, "v")
         kx, vx = k_ext.detach().requires_grad_(True), v_ext.detach().requires_grad_(True)
         sign = -1.0 if self.search.dist_type == "l2" else 1.0
         td = _time_dim(q)

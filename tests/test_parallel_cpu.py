@@ -81,3 +81,53 @@ def test_halo_exchange_gloo(world, T, wt):
     assert len(ret) == world
     for r in range(world):
         assert ret[r] == (True, True), (r, ret[r])
+
+
+def test_flat_shard_plan():
+    """flattened (B,T) sharding: C4 = B 2, T 32 over 8 ranks -> ranks 0-3 batch 0, ranks 4-7 batch 1"""
+    from stnls_b200.parallel import flat_shard
+    seen = []
+    for r in range(8):
+        bs, plan, ranks = flat_shard(2, 32, 3, 8, r)
+        assert (bs.start, bs.stop) == (r // 4, r // 4 + 1) and ranks == list(range(4 * (r // 4), 4 * (r // 4) + 4))
+        assert plan.world == 4 and plan.rank == r % 4 and plan.b - plan.a == 8
+        seen += [(bs.start, t) for t in range(plan.a, plan.b)]
+    assert sorted(seen) == [(b, t) for b in range(2) for t in range(32)]
+    bs, plan, ranks = flat_shard(4, 16, 1, 2, 1)     # fewer ranks than clips: whole clips, no halo
+    assert (bs.start, bs.stop) == (2, 4) and plan.world == 1 and ranks == [1]
+    with pytest.raises(ValueError):
+        flat_shard(3, 8, 1, 4, 0)
+
+
+def _worker_groups(rank, world, port, B, T, wt, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from stnls_b200.parallel import batch_groups, flat_shard
+        bs, plan, ranks = flat_shard(B, T, wt, world, rank)
+        group = batch_groups(B, world, rank)
+        full = th.randn(B, T, 3, 4, 5, generator=th.Generator().manual_seed(0))
+        x = full[bs, plan.a:plan.b].clone().requires_grad_(True)
+        ext = halo_exchange(x, plan, group)
+        ok_fwd = th.equal(ext, full[bs, plan.fa:plan.fb])
+        ext.sum().backward()
+        # every frame is counted once per rank of its batch group that holds it
+        exp = th.zeros_like(x)
+        for r in ranks:
+            p = ShardPlan(T, wt, len(ranks), r - ranks[0])
+            lo, hi = max(p.fa, plan.a), min(p.fb, plan.b)
+            if lo < hi:
+                exp[:, lo - plan.a:hi - plan.a] += 1
+        ret[rank] = (ok_fwd, bool(th.equal(x.grad, exp)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_halo_exchange_inside_batch_groups_gloo():
+    """world 4, B 2: two sub-groups of two ranks, the halo exchange stays inside each"""
+    ret = mp.Manager().dict()
+    mp.spawn(_worker_groups, args=(4, _free_port(), 2, 8, 2, ret), nprocs=4, join=True)
+    assert len(ret) == 4
+    for r in range(4):
+        assert ret[r] == (True, True), (r, ret[r])
