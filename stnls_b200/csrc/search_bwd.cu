@@ -381,7 +381,9 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   if (P.mode == 2) STNLS_REQUIRE(flows != nullptr, "search_backward: flows required with grad_flows");
   if (P.mode == 3) STNLS_REQUIRE(kselect && reflect, "search_backward: kselect/reflect required for refine flow grads");
   P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->nH * g->nW * P.nquad;
-  P.qagg = (P.nquad > 1 && P.nquad <= 32 && (P.nquad & (P.nquad - 1)) == 0 && !getenv("STNLS_NO_QAGG")) ? 1 : 0;
+  P.qagg = (P.nquad > 1 && P.nquad <= 32 && (P.nquad & (P.nquad - 1)) == 0 && getenv("STNLS_QAGG")) ? 1 : 0;   // opt-in: measured SLOWER
+  // (B200, r02_l vs r02_g: wpsum_backward c4s 74.9 -> 83.8 ms, search_backward 91.9 -> 98.5 ms; C2 0.294 -> 0.309 ms): the
+  // per-pair atomics were never the limiter, the butterflies and the convergence they force are pure overhead
   if (P.nthreads == 0 || K == 0) return STNLS_OK;
   // float modes, small launches: one thread per (query, neighbour, quad)
   // measured on B200 (profiles/README.md): with ps=3 the split form wins while the whole problem is a few

@@ -189,13 +189,22 @@ __device__ __noinline__ void tile_merge(unsigned* pk, int* px, int* cnt_ptr, uns
     }
   }
   unsigned last = 0xffffffffu;
+  constexpr int QW = 32 / FP;
+  const int sub = (threadIdx.x & 31) / FP;
+  // min over the FP lanes of a sub-group: one warp-wide redux.sync per sub-group (the other sub-groups contribute the
+  // neutral element) -- one instruction deep, where a shuffle butterfly is log2(FP) dependent steps
+  auto group_min = [&](unsigned v) {
+    unsigned r = 0xffffffffu;
+#pragma unroll
+    for (int gsub = 0; gsub < QW; gsub++) {
+      const unsigned mg = __reduce_min_sync(FULL_MASK, (sub == gsub) ? v : 0xffffffffu);
+      r = (sub == gsub) ? mg : r;
+    }
+    return r;
+  };
   for (int kk = 0; kk < LK; kk++) {
-    unsigned m = k[0];
-#pragma unroll
-    for (int off = FP / 2; off > 0; off >>= 1) m = min(m, __shfl_xor_sync(FULL_MASK, m, off));
-    unsigned wi = (k[0] == m) ? (unsigned)x[0] : 0x7fffffffu;
-#pragma unroll
-    for (int off = FP / 2; off > 0; off >>= 1) wi = min(wi, __shfl_xor_sync(FULL_MASK, wi, off));
+    const unsigned m = group_min(k[0]);
+    const unsigned wi = group_min((k[0] == m) ? (unsigned)x[0] : 0x7fffffffu);
     if (chl == 0) { pk[kk] = m; px[kk] = (int)wi; }
     last = m;
     const bool won = (m != 0xffffffffu) && (k[0] == m) && (x[0] == (int)wi);

@@ -575,7 +575,9 @@ static int agg_backward(float* gv_cl, float* grad_weights, float* grad_flows, co
   P.out = gv_cl; P.gweights = grad_weights; P.gflows = grad_flows; P.gout = gout_cl; P.v = v_cl;
   P.weights = weights; P.flows = flows; P.g = *g; P.o = *o; P.nquad = g->Fp / 4;
   P.nthreads = (int64_t)g->B * g->HD * g->Tq * g->nH * g->nW * P.nquad;
-  P.qagg = (P.nquad > 1 && P.nquad <= 32 && (P.nquad & (P.nquad - 1)) == 0 && !getenv("STNLS_NO_QAGG")) ? 1 : 0;
+  P.qagg = (P.nquad > 1 && P.nquad <= 32 && (P.nquad & (P.nquad - 1)) == 0 && getenv("STNLS_QAGG")) ? 1 : 0;   // opt-in: measured SLOWER
+  // (B200, r02_l vs r02_g: wpsum_backward c4s 74.9 -> 83.8 ms, search_backward 91.9 -> 98.5 ms; C2 0.294 -> 0.309 ms): the
+  // per-pair atomics were never the limiter, the butterflies and the convergence they force are pure overhead
   if (P.nthreads == 0 || o->K == 0) return STNLS_OK;
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_backward: too many threads for one launch");
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
