@@ -44,8 +44,15 @@ def assert_topk_equal(d, i, d_ref, i_ref, exact, atol=1e-4, rtol=1e-4, what="", 
     gap_next = th.full_like(d_ref, float("inf"))
     gap_prev[..., 1:] = (d_ref[..., 1:] - d_ref[..., :-1]).abs()
     gap_next[..., :-1] = gap_prev[..., 1:]
-    if not last_slot_clear:
-        gap_next[..., -1] = 0.0
+    # the last kept slot: the distance of the best candidate that was NOT kept is unknown, so "clearly separated" cannot
+    # be established there; a mismatch with matching distance is a near-tie across the K-th slot.  Such swaps are
+    # allowed but COUNTED: at most 2 + 1e-4 of the queries (last_slot_clear=False lifts the bound for the callers
+    # that count swaps themselves on million-query cases)
+    last_bad = fin[..., -1] & ((i.float() - i_ref.float()).abs().amax(-1)[..., -1] > 1e-3)
+    if last_slot_clear:
+        nlast = int(last_bad.sum())
+        assert nlast <= 2 + 1e-4 * last_bad.numel(), f"{what}: {nlast} index mismatches in the last kept slot"
+    gap_next[..., -1] = 0.0
     clear = fin & (gap_prev > 4 * tol) & (gap_next > 4 * tol)
     diff = (i.float() - i_ref.float()).abs().amax(-1)
     bad = clear & (diff > 1e-3)
