@@ -61,6 +61,7 @@ int launch_tile_l2(const FwdParams& P, const TileCfg& C, const CUtensorMap& map,
 #ifdef __CUDACC__
 
 constexpr int TILE_TQ = 8, TILE_NQ = 64, TILE_THREADS = 256, TILE_MAXWT = 16;
+constexpr int TILE_NQP = 65;   // per-query arrays: 64 queries + a dummy entry (index 64) for lanes without a query
 
 // ---- mbarrier / TMA (PTX) ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(unsigned a, unsigned count) {
@@ -159,20 +160,23 @@ __device__ __forceinline__ void tile_core(const float* __restrict__ bp, const in
 }
 
 // ---- pool compaction: the K best of a query's pool, sorted, to the head of the pool ------------------------------
-// Called by whole warps; each sub-group of FP lanes works on its own query (pk/px/cnt/thr are that query's) and the
-// butterflies use xor offsets < FP under the full mask.  Deliberately NOT inlined: it runs a few times per query,
+// Called by whole warps; each sub-group of GS lanes works on its own query (pk/px/cnt/thr are that query's); the group
+// minima are warp-wide redux.sync with the other groups' lanes neutral.  Deliberately NOT inlined: it runs a few times per query,
 // from inside the unrolled core, and must not add to the core's register pressure.
 constexpr int TILE_CAP = 64;   // pool entries per query
 
-template <int FP>
+template <int GS>
 __device__ __noinline__ void tile_merge(unsigned* pk, int* px, int* cnt_ptr, unsigned* thr_ptr, const int LK, const int chl) {
-  constexpr int E = TILE_CAP / FP;
-  const int cnt = *cnt_ptr;
+  constexpr int E = (TILE_CAP + GS - 1) / GS;
+  constexpr int QW = 32 / GS;                      // groups per warp; lanes beyond QW * GS idle along
+  const int sub = (threadIdx.x & 31) / GS;
+  const bool live = sub < QW;
+  const int cnt = live ? *cnt_ptr : 0;
   unsigned k[E];
   int x[E];
 #pragma unroll
   for (int j = 0; j < E; j++) {
-    const int e = chl + j * FP;
+    const int e = chl + j * GS;
     k[j] = (e < cnt) ? pk[e] : 0xffffffffu;
     x[j] = (e < cnt) ? px[e] : 0x7fffffff;
   }
@@ -189,9 +193,7 @@ __device__ __noinline__ void tile_merge(unsigned* pk, int* px, int* cnt_ptr, uns
     }
   }
   unsigned last = 0xffffffffu;
-  constexpr int QW = 32 / FP;
-  const int sub = (threadIdx.x & 31) / FP;
-  // min over the FP lanes of a sub-group: one warp-wide redux.sync per sub-group (the other sub-groups contribute the
+  // min over the GS lanes of a sub-group: one warp-wide redux.sync per sub-group (the other sub-groups contribute the
   // neutral element) -- one instruction deep, where a shuffle butterfly is log2(FP) dependent steps
   auto group_min = [&](unsigned v) {
     unsigned r = 0xffffffffu;
@@ -205,7 +207,7 @@ __device__ __noinline__ void tile_merge(unsigned* pk, int* px, int* cnt_ptr, uns
   for (int kk = 0; kk < LK; kk++) {
     const unsigned m = group_min(k[0]);
     const unsigned wi = group_min((k[0] == m) ? (unsigned)x[0] : 0x7fffffffu);
-    if (chl == 0) { pk[kk] = m; px[kk] = (int)wi; }
+    if (chl == 0 && live) { pk[kk] = m; px[kk] = (int)wi; }
     last = m;
     const bool won = (m != 0xffffffffu) && (k[0] == m) && (x[0] == (int)wi);
 #pragma unroll
@@ -215,7 +217,7 @@ __device__ __noinline__ void tile_merge(unsigned* pk, int* px, int* cnt_ptr, uns
     }
     if (won) { k[E - 1] = 0xffffffffu; x[E - 1] = 0x7fffffff; }
   }
-  if (chl == 0) {
+  if (chl == 0 && live) {
     *cnt_ptr = min(cnt, LK);
     *thr_ptr = (cnt >= LK) ? last : 0xffffffffu;   // admission threshold: the K-th best key once K candidates exist
   }
@@ -235,10 +237,16 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
   const stnls_geom& g = P.g;
   const stnls_search_opts& o = P.o;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  constexpr int QW = 32 / FP;                 // queries per warp
-  constexpr int NS = 32 / FP;                 // list entries per lane (NS * FP = 32 >= K)
-  const int sub = lane / FP, chl = lane % FP;
-  const unsigned submask = (FP == 32) ? 0xffffffffu : (((1u << (FP & 31)) - 1u) << (sub * FP));
+  // RAW: ps == 1 with the product distance -- the bilinear blend commutes with the channel contraction, so a lane owns
+  // one COLUMN of the (ws+1)^2 raw grid and does whole channel dot products itself (see the RAW pass below); otherwise
+  // lane = channel.  GS lanes work on one query, QW queries per warp (lanes beyond QW * GS idle along).
+  constexpr bool RAW = (PS == 1 && DIST == 0 && !HALF);
+  constexpr int GS = RAW ? WS + 1 : FP;
+  constexpr int QW = 32 / GS;                 // queries per warp
+  constexpr int NS = (32 + GS - 1) / GS;      // list entries per lane (NS * GS >= 32 >= K)
+  constexpr int NPASS = (TILE_NQ + 8 * QW - 1) / (8 * QW);
+  const int sub = lane / GS, chl = lane % GS;
+  const unsigned submask = (sub < QW) ? (((GS >= 32) ? 0xffffffffu : ((1u << (GS & 31)) - 1u)) << (sub * GS)) : 0u;
   const float s1 = o.stride1;
   const int s0 = o.stride0, po = o.patch_offset, W_t = P.W_t;
   const bool anchored = o.anchor_self != 0;
@@ -266,10 +274,10 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
   int* const stats = misc + 4;                           // [W_t][8]: min_h max_h sum_h min_w max_w sum_w count -
   int* const origin = stats + TILE_MAXWT * 8;            // [W_t][2]
   int* const state = origin + TILE_MAXWT * 2;            // [64]: 0 searched here, 1 deferred to direct_query, 2 outside the grid
-  int* const a_nls = state + TILE_NQ;                    // [64] anchor slot of the query
-  float* const adist = reinterpret_cast<float*>(a_nls + TILE_NQ);   // [64] distance of the anchor candidate
-  int* const pcnt = a_nls + 2 * TILE_NQ;                 // [64] pool entries in use
-  unsigned* const pthr = reinterpret_cast<unsigned*>(pcnt + TILE_NQ);   // [64] admission threshold (ordered key)
+  int* const a_nls = state + TILE_NQP;                   // [64] anchor slot of the query
+  float* const adist = reinterpret_cast<float*>(a_nls + TILE_NQP);   // [64] distance of the anchor candidate
+  int* const pcnt = a_nls + 2 * TILE_NQP;                // [64] pool entries in use
+  unsigned* const pthr = reinterpret_cast<unsigned*>(pcnt + TILE_NQP);   // [64] admission threshold (ordered key)
   float* const akey = reinterpret_cast<float*>(smem + C.off_akey);   // [W_t][64] (anchored only)
   int* const apos = reinterpret_cast<int*>(smem + C.off_apos);
   const unsigned mbar0 = (unsigned)__cvta_generic_to_shared(misc);
@@ -286,9 +294,9 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
   };
 
   // ---- prologue 1: init, query tile ----
-  if (tid < TILE_NQ) {
+  if (tid < TILE_NQP) {
     QueryCtx c;
-    state[tid] = query_ctx(tid, c) ? 0 : 2;
+    state[tid] = (tid < TILE_NQ && query_ctx(tid, c)) ? 0 : 2;
     adist[tid] = invalid;
     a_nls[tid] = 0;
     pcnt[tid] = 0;
@@ -432,10 +440,13 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
       }
       __syncthreads();
     }
-    for (int pass = 0; pass < TILE_NQ / (8 * QW); pass++) {
-      const int ql = (pass * 8 + warp) * QW + sub;
+    for (int pass = 0; pass < NPASS; pass++) {
+      const int qlr = (pass * 8 + warp) * QW + sub;
+      const bool qvalid = sub < QW && qlr < TILE_NQ;
+      const int ql = qvalid ? qlr : TILE_NQ;     // per-query state (the dummy entry for lanes without a query)
+      const int qls = qvalid ? qlr : 0;          // read-only tables
       const bool active = state[ql] == 0;
-      const float4 dsc = desc[st * 64 + ql];
+      const float4 dsc = desc[st * 64 + qls];
       const unsigned masks = __float_as_uint(dsc.z);
       const unsigned hm = masks & 0xffffu, wm = masks >> 16;
       const int an = a_nls[ql];
@@ -443,10 +454,76 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
       int* const px = pooli + ql * TILE_CAP;
       int cnt = pcnt[ql];            // register copies, uniform inside the sub-group
       unsigned thr = pthr[ql];
+      if constexpr (RAW) {
+        // ---- ps == 1, product: d(i,j) = bilinear blend of the raw dot products D(x,y) = <q, k_raw(r0+x, c0+y)> on the
+        // (ws+1)^2 integer grid.  Lane = grid column y, loop over grid rows: 4 LDS.128 + Fp FMAs per grid point, no sum
+        // across lanes; the right neighbour's D comes by one shuffle, the previous row's blend stays in a register.
+        // Lanes walk the channel quads in an order rotated by their column so that the 16-byte reads of neighbouring
+        // columns (one pixel = Fp*4 bytes apart) fall on different banks.
+        constexpr int NQD = FP / 4;
+        const int y = chl;
+        const int rot = (y >> 1) & (NQD - 1);
+        float4 qr[NQD];
+        {
+          const float* qp = qt + (((qls >> 3) * s0) * C.QT + (qls & 7) * s0) * FP;
+#pragma unroll
+          for (int t2 = 0; t2 < NQD; t2++) qr[t2] = *reinterpret_cast<const float4*>(qp + (((t2 + rot) & (NQD - 1)) << 2));
+        }
+        const float flh = floorf(dsc.x), flw = floorf(dsc.y);
+        const float fh = dsc.x - flh, fw = dsc.y - flw, gh0 = 1.f - fh, gw0 = 1.f - fw;
+        const int r0 = active ? (int)flh - oh : 0, c0 = active ? (int)flw - ow : 0;
+        const float* bp = box + (r0 * C.BW + c0 + y) * FP;
+        float Hprev = 0.f;
+#pragma unroll
+        for (int x = 0; x <= WS; x++) {
+          const float* pp = bp + x * rowpitch;
+          float D = 0.f;
+#pragma unroll
+          for (int t2 = 0; t2 < NQD; t2++) {
+            const float4 kv = *reinterpret_cast<const float4*>(pp + (((t2 + rot) & (NQD - 1)) << 2));
+            D = fmaf(qr[t2].x, kv.x, D); D = fmaf(qr[t2].y, kv.y, D); D = fmaf(qr[t2].z, kv.z, D); D = fmaf(qr[t2].w, kv.w, D);
+          }
+          const float Dn = __shfl_down_sync(FULL_MASK, D, 1);
+          const float H = fmaf(fw, Dn, gw0 * D);
+          if (x >= 1) {
+            float d = fmaf(fh, H, gh0 * Hprev);
+            const int wi = x - 1, wj = y;
+            unsigned key = 0xffffffffu;
+            int eff = 0;
+            if (y < WS) {
+              if (!((hm >> wi) & (wm >> wj) & 1u)) d = invalid;
+              eff = st * WS * WS + wi * WS + wj;
+              key = min(f2ord_t(-d + 0.f), 0xfffffffeu);
+              if (anchored) {
+                if (eff == an) { adist[ql] = d; key = 0xffffffffu; }
+                else if (eff == 0) eff = an;
+              }
+            }
+            if (__any_sync(FULL_MASK, cnt + GS > TILE_CAP)) {
+              if (chl == 0) pcnt[ql] = cnt;
+              __syncwarp();
+              tile_merge<GS>(pk, px, pcnt + ql, pthr + ql, LK, chl);
+              cnt = pcnt[ql];
+              thr = pthr[ql];
+            }
+            const bool pass_ = active && key <= thr && key != 0xffffffffu;
+            const unsigned mine = __ballot_sync(FULL_MASK, pass_) & submask;
+            if (pass_) {
+              const int slot = cnt + __popc(mine & ((1u << lane) - 1u));
+              pk[slot] = key;
+              px[slot] = eff;
+            }
+            cnt += __popc(mine);
+          }
+          Hprev = H;
+        }
+        if (chl == 0) pcnt[ql] = cnt;
+        continue;
+      }
       // query patch, this lane's channel
       float qv[PS * PS];
       {
-        const float* qp = qt + (((ql >> 3) * s0) * C.QT + (ql & 7) * s0) * FP + chl;
+        const float* qp = qt + (((qls >> 3) * s0) * C.QT + (qls & 7) * s0) * FP + (RAW ? 0 : chl);
 #pragma unroll
         for (int pi = 0; pi < PS; pi++)
 #pragma unroll
@@ -496,7 +573,7 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
             if (__any_sync(FULL_MASK, cnt + FP > TILE_CAP)) {
               if (chl == 0) pcnt[ql] = cnt;
               __syncwarp();
-              tile_merge<FP>(pk, px, pcnt + ql, pthr + ql, LK, chl);
+              tile_merge<GS>(pk, px, pcnt + ql, pthr + ql, LK, chl);
               cnt = pcnt[ql];
               thr = pthr[ql];
             }
@@ -530,11 +607,12 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
 
   // ---- outputs: the sorted list -> dists / inds ----
   float* const inds_out = reinterpret_cast<float*>(P.inds);
-  for (int pass = 0; pass < TILE_NQ / (8 * QW); pass++) {
-    const int ql = (pass * 8 + warp) * QW + sub;
+  for (int pass = 0; pass < NPASS; pass++) {
+    const int qlr = (pass * 8 + warp) * QW + sub;
+    const int ql = (sub < QW && qlr < TILE_NQ) ? qlr : TILE_NQ;
     const int an = a_nls[ql];
     __syncwarp();
-    tile_merge<FP>(poolk + ql * TILE_CAP, pooli + ql * TILE_CAP, pcnt + ql, pthr + ql, LK, chl);
+    tile_merge<GS>(poolk + ql * TILE_CAP, pooli + ql * TILE_CAP, pcnt + ql, pthr + ql, LK, chl);
     if (state[ql] != 0) continue;
     QueryCtx c;
     query_ctx(ql, c);
@@ -548,7 +626,7 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
     }
 #pragma unroll
     for (int s = 0; s < NS; s++) {
-      const int e = s * FP + chl;
+      const int e = s * GS + chl;
       if (e >= LK) continue;
       const unsigned mk = poolk[ql * TILE_CAP + e];
       const int mi = pooli[ql * TILE_CAP + e];

@@ -40,8 +40,8 @@ int carve(const FwdParams& P, TileCfg& C, int nbuf) {
   C.box_bytes = round_up(C.box_tx, 128);
   int off = nbuf * C.box_bytes;
   C.off_desc = off; off += TILE_NQ * P.W_t * 16;
-  C.off_pk = off; off += TILE_NQ * TILE_CAP * 4;   // per-query pool: keys ...
-  C.off_pi = off; off += TILE_NQ * TILE_CAP * 4;   // ... and candidate indices
+  C.off_pk = off; off += TILE_NQP * TILE_CAP * 4;   // per-query pool: keys ...
+  C.off_pi = off; off += TILE_NQP * TILE_CAP * 4;   // ... and candidate indices
   C.QT = (TILE_TQ - 1) * P.o.stride0 + P.o.ps;
   C.off_qt = off; off += round_up(C.QT * C.QT * Fp * 4, 16);
   // transpose scratch: candidates of one flush x (Fp + 4) floats per query; the query stride keeps the sub-groups of a
@@ -58,8 +58,9 @@ int carve(const FwdParams& P, TileCfg& C, int nbuf) {
   C.q_stride = nv * C.cand_pitch;
   while ((C.q_stride & 31) != (Fp & 31)) C.q_stride++;
   C.scr_warp = QW * C.q_stride;
-  C.off_scr = off; off += (TILE_THREADS / 32) * C.scr_warp * 4;
-  C.off_misc = off; off += (4 + TILE_MAXWT * 8 + TILE_MAXWT * 2 + 5 * TILE_NQ) * 4;
+  const bool rawdot = P.o.ps == 1 && P.o.dist_type == 0 && !half;   // that variant sums channels inside a lane: no scratch
+  C.off_scr = off; off += rawdot ? 0 : (TILE_THREADS / 32) * C.scr_warp * 4;
+  C.off_misc = off; off += (4 + TILE_MAXWT * 8 + TILE_MAXWT * 2 + 5 * TILE_NQP) * 4;
   C.off_akey = off; off += P.o.anchor_self ? TILE_NQ * P.W_t * 4 : 0;
   C.off_apos = off; off += P.o.anchor_self ? TILE_NQ * P.W_t * 4 : 0;
   C.smem_bytes = round_up(off, 128);
