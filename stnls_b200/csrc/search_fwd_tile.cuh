@@ -477,12 +477,15 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
 #pragma unroll
         for (int x = 0; x <= WS; x++) {
           const float* pp = bp + x * rowpitch;
-          float D = 0.f;
+          float Dq[NQD];   // one short FMA chain per channel quad (a single 4*NQD-deep chain is latency-bound)
 #pragma unroll
           for (int t2 = 0; t2 < NQD; t2++) {
             const float4 kv = *reinterpret_cast<const float4*>(pp + (((t2 + rot) & (NQD - 1)) << 2));
-            D = fmaf(qr[t2].x, kv.x, D); D = fmaf(qr[t2].y, kv.y, D); D = fmaf(qr[t2].z, kv.z, D); D = fmaf(qr[t2].w, kv.w, D);
+            Dq[t2] = fmaf(qr[t2].w, kv.w, fmaf(qr[t2].z, kv.z, fmaf(qr[t2].y, kv.y, qr[t2].x * kv.x)));
           }
+          float D = Dq[0];
+#pragma unroll
+          for (int t2 = 1; t2 < NQD; t2++) D += Dq[t2];
           const float Dn = __shfl_down_sync(FULL_MASK, D, 1);
           const float H = fmaf(fw, Dn, gw0 * D);
           if (x >= 1) {
