@@ -31,9 +31,11 @@ def build(force=False):
     if (not force) and os.path.exists(_SO) and os.path.getmtime(_SO) >= os.path.getmtime(src):
         return _SO
     os.makedirs(os.path.dirname(_SO), exist_ok=True)
+    tmp = _SO + f".tmp{os.getpid()}"   # built aside and moved into place: concurrent ranks never load a partial file
     cmd = ["gcc", "-O2", "-fPIC", "-shared", "-fopenmp", "-ffp-contract=off", "-std=gnu11",
-           "-o", _SO, src, "-lm"]
+           "-o", tmp, src, "-lm"]
     subprocess.check_call(cmd)
+    os.replace(tmp, _SO)
     return _SO
 
 

@@ -48,13 +48,13 @@ def lib():
         return _lib
     path = _build.LIB
     if _build.needs_build():
+        # sources differ from the ones the library was built from (or there is no library): build, and fail LOUDLY if
+        # that is impossible -- a stale library would run old kernels behind a newer header
         try:
             _build.build()
-        except Exception as exc:  # no nvcc / compile failure: fail loudly, never fall back
-            if not os.path.exists(path):
-                raise ImportError(
-                    "stnls_b200: libstnls_b200.so is missing and could not be built "
-                    f"({exc}); run `python -m stnls_b200.build`") from exc
+        except Exception as exc:
+            raise ImportError("stnls_b200: libstnls_b200.so is missing or older than its sources and could not be "
+                              f"built ({exc}); run `python -m stnls_b200.build`") from exc
     L = ctypes.CDLL(path)
     L.stnls_last_error.restype = ctypes.c_char_p
     P = ctypes.POINTER
