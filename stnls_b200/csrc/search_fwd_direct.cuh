@@ -117,6 +117,8 @@ __device__ __noinline__ void direct_query(const FwdParams& P, const int64_t wq, 
       }
       // stream into the list
       float key = (DIST == 0) ? -d : d;
+      if (key != key) key = INFINITY;   // NaN distance (non-finite inputs): ranks last instead of never being inserted,
+                                        // so every output slot is written (the reference returns a full sorted list)
       bool want = active && !(anchored && eff == 0);
       float wk = __shfl_sync(FULL_MASK, tk.key, max(Klist - 1, 0));
       int wp = __shfl_sync(FULL_MASK, tk.pos, max(Klist - 1, 0));

@@ -106,10 +106,16 @@ __device__ __forceinline__ float acc1(float acc, float qv, float kv) {
   return fmaf(d, d, acc);
 }
 
-template <int WH, int WW, int PS, int DIST, int FP, int G, class Flush>
+// Finished candidates are handed to `flush(lin0, nv, vals)` in batches of FL (lin0 = row-major index of vals[0] inside
+// this sub-window): FL = the whole window when it is small, else the number of lanes that sum channels (FP), so that
+// every reader lane has a candidate in every flush (rows of 9 candidates would leave 7 of 16 lanes idle).
+__host__ __device__ constexpr int tile_flush_size(int WH, int WW, int FP) { return (WH * WW <= 2 * FP) ? WH * WW : FP; }
+
+template <int WH, int WW, int PS, int DIST, int FP, int FL, class Flush>
 __device__ __forceinline__ void tile_core(const float* __restrict__ bp, const int rowpitch, const float fh, const float fw,
                                           const float (&qv)[PS * PS], Flush&& flush) {
   constexpr int MR = WH + PS - 1, MC = WW + PS - 1;
+  constexpr int PMAX = FL + WW;   // pending finished candidates: fewer than FL left over + one new row
   const float gh0 = 1.f - fh, gw0 = 1.f - fw;
   float prev[MC + 1], cur[MC + 1];
 #pragma unroll
@@ -119,7 +125,8 @@ __device__ __forceinline__ void tile_core(const float* __restrict__ bp, const in
   for (int s = 0; s < PS; s++)
 #pragma unroll
     for (int j = 0; j < WW; j++) acc[s][j] = 0.f;
-  float fin[G * WW];
+  float pend[PMAX];
+  int np = 0, lin0 = 0;   // compile-time values once the row loop is unrolled
 #pragma unroll
   for (int x = 0; x < MR; x++) {
     const float* rp = bp + (x + 1) * rowpitch;
@@ -149,10 +156,21 @@ __device__ __forceinline__ void tile_core(const float* __restrict__ bp, const in
       const int i = x - (PS - 1);   // candidate row i is complete
 #pragma unroll
       for (int j = 0; j < WW; j++) {
-        fin[(i % G) * WW + j] = acc[i % PS][j];
+        pend[np + j] = acc[i % PS][j];
         acc[i % PS][j] = 0.f;
       }
-      if ((i % G) == G - 1 || i == WH - 1) flush(i - (i % G), (i % G) + 1, fin);
+      np += WW;
+#pragma unroll
+      for (int rep = 0; rep < (PMAX + FL - 1) / FL; rep++) {
+        if (np >= FL || (i == WH - 1 && np > 0)) {
+          const int nv = np < FL ? np : FL;
+          flush(lin0, nv, pend);
+#pragma unroll
+          for (int j = 0; j < PMAX - FL; j++) pend[j] = pend[j + FL];
+          lin0 += nv;
+          np -= nv;
+        }
+      }
     }
 #pragma unroll
     for (int y = 0; y <= MC; y++) prev[y] = cur[y];
@@ -222,11 +240,6 @@ __device__ __noinline__ void tile_merge(unsigned* pk, int* px, int* cnt_ptr, uns
     *thr_ptr = (cnt >= LK) ? last : 0xffffffffu;   // admission threshold: the K-th best key once K candidates exist
   }
   __syncwarp();
-}
-
-// rows of finished candidates handed over per flush: whole small windows at once, single rows of wide ones
-__host__ __device__ constexpr int tile_flush_rows(int WH, int WW) {
-  return (WH * WW <= 16) ? WH : (2 * WW <= 16 && WH >= 2) ? 2 : 1;
 }
 
 template <int DIST, int PS, int WS, bool HALF, int FP>
@@ -536,20 +549,19 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
       // one integer-spaced (sub-)window: candidates (eh + step*i, ew + step*j) of the ws x ws window
       auto run_window = [&](auto WHc, auto WWc, const int eh, const int ew) {
         constexpr int WH = decltype(WHc)::value, WW = decltype(WWc)::value;
-        constexpr int G = tile_flush_rows(WH, WW);
+        constexpr int FL = tile_flush_size(WH, WW, FP);
         constexpr int STEP = HALF ? 2 : 1;
         const float ph = HALF ? dsc.x + 0.5f * (float)eh : dsc.x, pw = HALF ? dsc.y + 0.5f * (float)ew : dsc.y;
         const float flh = floorf(ph), flw = floorf(pw);
         const int r0 = active ? (int)flh - oh : 0, c0 = active ? (int)flw - ow : 0;
         const float* bp = box + (r0 * C.BW + c0) * FP + chl;
-        auto flush = [&](const int ibase, const int nrows, const float* fin) {
-          const int nv = nrows * WW;
+        auto flush = [&](const int lin0, const int nv, const float* vals) {
 #pragma unroll
-          for (int v = 0; v < G * WW; v++)
-            if (v < nv) scr[v * C.cand_pitch + chl] = fin[v];
+          for (int v = 0; v < FL; v++)
+            if (v < nv) scr[v * C.cand_pitch + chl] = vals[v];
           __syncwarp();
 #pragma unroll
-          for (int m = 0; m < (G * WW + FP - 1) / FP; m++) {
+          for (int m = 0; m < (FL + FP - 1) / FP; m++) {
             const int v = chl + m * FP;
             unsigned key = 0xffffffffu;
             int eff = 0;
@@ -561,8 +573,9 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
                 const float4 x4 = sp[c4];
                 d += (x4.x + x4.y) + (x4.z + x4.w);
               }
-              const int vi = v / WW, vj = v - vi * WW;
-              const int wi = eh + STEP * (ibase + vi), wj = ew + STEP * vj;
+              const int lin = lin0 + v;
+              const int vi = lin / WW, vj = lin - vi * WW;
+              const int wi = eh + STEP * vi, wj = ew + STEP * vj;
               if (!((hm >> wi) & (wm >> wj) & 1u)) d = invalid;
               eff = st * WS * WS + wi * WS + wj;
               key = min(f2ord_t(((DIST == 0) ? -d : d) + 0.f), 0xfffffffeu);
@@ -591,7 +604,7 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
           }
           __syncwarp();
         };
-        tile_core<WH, WW, PS, DIST, FP, G>(bp, rowpitch, ph - flh, pw - flw, qv, flush);
+        tile_core<WH, WW, PS, DIST, FP, FL>(bp, rowpitch, ph - flh, pw - flw, qv, flush);
       };
       if (!HALF) {
         run_window(std::integral_constant<int, WS>(), std::integral_constant<int, WS>(), 0, 0);

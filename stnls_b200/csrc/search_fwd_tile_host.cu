@@ -52,7 +52,7 @@ int carve(const FwdParams& P, TileCfg& C, int nbuf) {
   for (int a = 0; a < 2; a++)
     for (int b = 0; b < 2; b++) {
       const int wh = a ? WO : WE, ww = b ? WO : WE;
-      if (wh > 0 && ww > 0 && tile_flush_rows(wh, ww) * ww > nv) nv = tile_flush_rows(wh, ww) * ww;
+      if (wh > 0 && ww > 0 && tile_flush_size(wh, ww, Fp) > nv) nv = tile_flush_size(wh, ww, Fp);
     }
   C.cand_pitch = Fp + 4;
   C.q_stride = nv * C.cand_pitch;

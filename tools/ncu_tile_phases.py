@@ -28,7 +28,7 @@ marks = [("core (interpolate + accumulate)", find("__device__ __forceinline__ fl
          ("prologue (geometry, q tile, TMA issue)", find("// ---- which tile ----"), loop),
          ("frame head (mbarrier wait, mirror fill)", loop, find("for (int pass = 0;", loop)),
          ("q patch load", find("// query patch, this lane's channel"), find("// one integer-spaced (sub-)window")),
-         ("flush (transpose-sum, key, append)", find("auto flush = [&]"), find("tile_core<WH, WW, PS, DIST, FP, G>(bp")),
+         ("flush (transpose-sum, key, append)", find("auto flush = [&]"), find("tile_core<WH, WW, PS, DIST, FP, FL>(bp")),
          ("output (final compaction call, dists/inds)", find("// ---- outputs: the sorted list"), find("// ---- queries this tile could not stage"))]
 rep = sys.argv[1]; units = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
 L = lines(rep)
