@@ -12,6 +12,7 @@
 #include "search_fwd_direct.cuh"
 #include "search_fwd_tab.cuh"
 #include "search_fwd_tile.cuh"
+#include "search_fwd_refine_chan.cuh"
 
 using namespace stnls_fwd;
 
@@ -185,6 +186,14 @@ extern "C" int stnls_search_forward(const float* q_cl, const float* k_cl, const 
     STNLS_REQUIRE(rc >= 0, "search_forward: cannot reserve shared memory for the tile kernel");
     if (rc == 1) {
       STNLS_CHECK_LAUNCH("search_forward(tile)");
+      return STNLS_OK;
+    }
+  }
+  if (refine) {
+    // float RefineSearch: the channel-parallel kernel (lane = channel, raw pixels read once per input offset)
+    const int rc = launch_refine_chan(P, st);
+    if (rc == 1) {
+      STNLS_CHECK_LAUNCH("search_forward(refine, channel-parallel)");
       return STNLS_OK;
     }
   }

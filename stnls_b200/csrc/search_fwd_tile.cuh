@@ -586,7 +586,7 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
               }
             }
             // room for one entry per lane?  (rare; warp-uniform, each sub-group compacts its own pool)
-            if (__any_sync(FULL_MASK, cnt + FP > TILE_CAP)) {
+            if (__any_sync(FULL_MASK, cnt + (FL < FP ? FL : FP) > TILE_CAP)) {   // room for what one round can append
               if (chl == 0) pcnt[ql] = cnt;
               __syncwarp();
               tile_merge<GS>(pk, px, pcnt + ql, pthr + ql, LK, chl);

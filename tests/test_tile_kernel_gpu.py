@@ -108,3 +108,38 @@ def test_tile_kernel_non_finite_flows(cuda, oracle):
     fin = th.isfinite(d_ref)
     assert bool((th.isfinite(d1.cpu()) == fin).all())
     assert th.allclose(d1.cpu()[fin], d_ref[fin], atol=1e-4, rtol=1e-4)
+
+
+REFINE_CASES = [
+    # name, F, HD, H, W, T, Ks, wr, ps, K, stride0, dist
+    ("c5like_fp32_l2", 32, 1, 40, 44, 3, 30, 3, 3, 30, 2, "l2"),
+    ("fp16_prod", 32, 2, 33, 37, 3, 12, 3, 3, 9, 1, "prod"),
+    ("fp8_l2", 16, 2, 36, 34, 4, 7, 3, 3, 32, 1, "l2"),
+    ("fp16_ps1", 16, 1, 35, 35, 3, 9, 3, 1, 5, 1, "l2"),
+    ("fp16_wr1", 32, 2, 34, 36, 3, 20, 1, 3, 6, 1, "prod"),
+]
+
+
+@pytest.mark.parametrize("c", REFINE_CASES, ids=[c[0] for c in REFINE_CASES])
+def test_refine_channel_kernel_vs_oracle(c, cuda, oracle):
+    """RefineSearch forward: the channel-parallel kernel (csrc/search_fwd_refine_chan.cuh) and the table kernel against
+    the CPU oracle -- offsets that leave the frame / point at its border take the generic path inside the launch"""
+    name, F, HD, H, W, T, Ks, wr, ps, K, s0, dist = c
+    g = th.Generator().manual_seed(hash(name) % 1000)
+    q, k = [th.randn(1, T, F, H, W, generator=g) for _ in range(2)]
+    nH, nW = (H - 1) // s0 + 1, (W - 1) // s0 + 1
+    fl = th.zeros(1, HD, T, nH, nW, Ks, 3)
+    fl[..., 0] = th.randint(-1, 2, fl[..., 0].shape, generator=g).float()
+    fl[..., 1:] = th.randint(-6, 7, fl[..., 1:].shape, generator=g).float() + th.rand(fl[..., 1:].shape, generator=g) / 2 + 0.2
+    kw = dict(nheads=HD, stride0=s0, stride1=1, dist_type=dist, self_action=None, itype="float")
+    dr, ir, ksr, rfr = oracle.refine_forward(q, k, fl, 3, 1, wr, K, -1, ps, **kw)
+    search = stnls_b200.search.RefineSearch(3, 1, wr, K, -1, ps, **kw)
+    for chan in ("1", "0"):
+        os.environ["STNLS_REFINE_CHAN"] = chan
+        try:
+            d, i = search(q.to(cuda), k.to(cuda), fl.to(cuda))
+        finally:
+            os.environ.pop("STNLS_REFINE_CHAN", None)
+        assert_topk_equal(d, i, dr, ir, exact=False, what=f"{name} [chan={chan}]", last_slot_clear=False)
+        nsw = int(((i.cpu() - ir).abs().amax(-1) > 1e-3).sum())
+        assert nsw <= 4 + 1e-4 * ir[..., 0].numel(), f"{name} [chan={chan}]: {nsw} index swaps against the oracle"

@@ -24,7 +24,7 @@ def find(pat, start=0):
     raise SystemExit("marker not found: " + pat)
 loop = find("for (int st = 0; st < W_t; st++) {", find("// ---- frame slots: TMA box"))
 marks = [("core (interpolate + accumulate)", find("__device__ __forceinline__ float acc1"), find("// ---- pool compaction")),
-         ("tile_merge (pool compaction)", find("// ---- pool compaction"), find("// rows of finished candidates handed over per flush")),
+         ("tile_merge (pool compaction)", find("// ---- pool compaction"), find("__global__ void __launch_bounds__(TILE_THREADS")),
          ("prologue (geometry, q tile, TMA issue)", find("// ---- which tile ----"), loop),
          ("frame head (mbarrier wait, mirror fill)", loop, find("for (int pass = 0;", loop)),
          ("q patch load", find("// query patch, this lane's channel"), find("// one integer-spaced (sub-)window")),
