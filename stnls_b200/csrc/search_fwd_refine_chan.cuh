@@ -24,7 +24,7 @@ int launch_refine_chan(const FwdParams& P, cudaStream_t st);
 #ifdef __CUDACC__
 
 template <int DIST, int PS, int WR, int FP>
-__global__ void __launch_bounds__(256, 2) refine_chan_kernel(const __grid_constant__ FwdParams P) {
+__global__ void __launch_bounds__(256, 3) refine_chan_kernel(const __grid_constant__ FwdParams P) {
   constexpr int QW = 32 / FP;            // queries per warp
   constexpr int NQ = 8 * QW;             // queries per CTA
   constexpr int NS = 32 / FP;            // list entries per lane
