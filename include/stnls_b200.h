@@ -198,6 +198,23 @@ int stnls_seg_copy(float* const* dst, const float* const* src, const int64_t* nf
  * 2*16*iters*256*blocks.  bench.py times it with CUDA events for the fp32 roofline denominator. */
 int stnls_ffma_peak(float* sink, int blocks, int iters, stnls_stream_t stream);
 
+/* ---- allocation-free forward search on planar videos ---------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as  stnls_pack_cl(q) + stnls_pack_cl(k) + stnls_search_forward(..., kselect = NULL, reflect = NULL),
+ * but the two channels-last copies live in a device array built into the library (STNLS_NOALLOC_MAX_BYTES, held by
+ * every GPU that loads the library until exit) instead of caller-allocated buffers.  No cudaMalloc / cudaFree /
+ * allocating routine is called.
+ *  q (B, T, HD*F, qH, qW), k (B, T, HD*F, kH, kW): contiguous planar videos of the whole clip; frames
+ *  [tq0, tq0+Tq) of q and [tk0, tk0+Tk) of k are used.  flows / dists / inds: as for stnls_search_forward.
+ *  Limit: round256(B*HD*Tq*qH*qW*Fp*4) + round256(B*HD*Tk*kH*kW*Fp*4) <= STNLS_NOALLOC_MAX_BYTES, else STNLS_EINVAL.
+ *  The array is shared by every call on a GPU and keeps the last call's contents (each call overwrites all it reads,
+ *  nothing needs clearing): calls that overlap on one GPU -- two streams, two threads -- RACE; serialise them.
+ *  The device that owns the buffers must be current, as for every other entry point.                              */
+#define STNLS_NOALLOC_MAX_BYTES (32u << 20)
+int stnls_search_forward_planar_noalloc(const float* q, const float* k, const void* flows, float* dists, void* inds,
+                                        const stnls_geom* g, const stnls_search_opts* o, stnls_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,7 +37,8 @@ EXPORTS = ["stnls_last_error", "stnls_version", "stnls_pack_cl", "stnls_unpack_c
            "stnls_wpsum_backward", "stnls_gather_forward", "stnls_gather_backward",
            "stnls_search_flow_forward", "stnls_search_flow_backward",
            "stnls_softmax_forward", "stnls_softmax_backward", "stnls_anchor_self_time",
-           "stnls_overlap_counts", "stnls_add_inplace", "stnls_ffma_peak", "stnls_seg_copy"]
+           "stnls_overlap_counts", "stnls_add_inplace", "stnls_ffma_peak", "stnls_seg_copy",
+           "stnls_search_forward_planar_noalloc"]
 
 _lib = None
 
@@ -61,6 +62,7 @@ def lib():
     L.stnls_pack_cl.argtypes = [c_vp, c_vp] + [c_int] * 8 + [c_i64] * 4 + [c_vp, c_vp, c_vp]
     L.stnls_unpack_cl.argtypes = [c_vp, c_vp] + [c_int] * 8 + [c_i64] * 4 + [c_int, c_vp]
     L.stnls_search_forward.argtypes = [c_vp] * 7 + [P(Geom), P(SearchOpts), c_vp]
+    L.stnls_search_forward_planar_noalloc.argtypes = [c_vp] * 5 + [P(Geom), P(SearchOpts), c_vp]
     L.stnls_search_backward.argtypes = [c_vp] * 11 + [c_int, P(Geom), P(SearchOpts), c_vp]
     L.stnls_wpsum_forward.argtypes = [c_vp] * 6 + [P(Geom), P(AggOpts), c_vp]
     L.stnls_wpsum_backward.argtypes = [c_vp] * 7 + [P(Geom), P(AggOpts), c_vp]

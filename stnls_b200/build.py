@@ -15,7 +15,7 @@ LIB = os.path.join(_HERE, "libstnls_b200.so")
 STAMP = LIB + ".srchash"
 SOURCES = ["errors.cu", "layout.cu", "search_fwd.cu", "search_fwd_tab_nls_int.cu", "search_fwd_tab_nls_float.cu",
            "search_fwd_tab_ref_int.cu", "search_fwd_tab_ref_float.cu", "search_fwd_tile_host.cu", "search_fwd_tile_prod.cu",
-           "search_fwd_tile_l2.cu", "search_fwd_refine_chan.cu", "search_bwd.cu", "wpsum.cu", "search_flow.cu", "normz.cu", "anchor.cu", "peak.cu"]
+           "search_fwd_tile_l2.cu", "search_fwd_refine_chan.cu", "search_bwd.cu", "wpsum.cu", "search_flow.cu", "normz.cu", "anchor.cu", "peak.cu", "noalloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
