@@ -42,6 +42,42 @@ __device__ __forceinline__ int64_t divmod(int64_t x, int d, int& rem) {
   return q;
 }
 
+// Division by a launch-constant divisor as multiply-high + shift (3 instructions instead of the ~20 of a 32-bit
+// hardware-less division): valid for dividends below 2^31.  mul == 0 encodes d == 1.
+struct FastDiv {
+  unsigned d, mul, shr;
+};
+inline FastDiv make_fastdiv(int d_) {
+  FastDiv f;
+  f.d = (unsigned)d_; f.mul = 0; f.shr = 0;
+  if (d_ > 1) {
+    unsigned l = 0;
+    while ((1ull << l) < (unsigned long long)d_) l++;          // ceil(log2 d)
+    const unsigned p = 31 + l;
+    f.mul = (unsigned)((((unsigned long long)1 << p) + f.d - 1) / f.d);
+    f.shr = p - 32;
+  }
+  return f;
+}
+// Launch shape of the per-(query, ...) kernels: grid.x covers the threads of ONE frame (n, t) -- fewer than 2^31, so the
+// index inside the frame is decoded with FastDivs -- and grid.y/z enumerate the frames.  false: a frame alone has 2^31
+// threads or more (the caller falls back to the flat 64-bit index).
+inline bool frame_grid(int64_t per_frame, int64_t frames, int tpb, dim3& grid) {
+  if (per_frame <= 0 || frames <= 0 || per_frame >= (1LL << 31) || frames >= (1LL << 30)) return false;
+  const unsigned gy = (unsigned)(frames < 32768 ? frames : 32768);
+  const unsigned gz = (unsigned)((frames + gy - 1) / gy);
+  if (gz > 65535) return false;
+  grid = dim3((unsigned)((per_frame + tpb - 1) / tpb), gy, gz);
+  return true;
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned fdivmod(unsigned x, const FastDiv& f, int& rem) {
+  const unsigned q = f.mul ? (__umulhi(x, f.mul) >> f.shr) : x;
+  rem = (int)(x - q * f.d);
+  return q;
+}
+#endif
+
 // -------- reflect-once bounds (shared_kernel.cu:49-60) ---------------------------------------
 __device__ __forceinline__ int bnd(int v, int lim) {
   if (v < 0) return -v;
@@ -113,8 +149,8 @@ __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpre
 // vector reduction into global memory: one 16-byte RED instead of four scalar atomics (sm_90+)
 __device__ __forceinline__ void red_add4(float* addr, float4 v) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z),
-               "f"(v.w)
-               : "memory");
+               "f"(v.w));   // no "memory" clobber: the accumulators never alias what a kernel reads, so loads may be
+                            // scheduled across the REDs (they are fire-and-forget)
 }
 
 __device__ __forceinline__ float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }

@@ -35,6 +35,10 @@ struct BwdParams {
   stnls_geom g;
   stnls_search_opts o;
   int K, mode, nquad, W_t, fast3, ksplit, qagg;
+  int idx32;                                  // launch shape of frame_grid(): thread index decoded with the FastDivs
+  unsigned per_frame, frames;
+  unsigned gx, gy, gz;
+  FastDiv fquad, fK, fnW, fTq, fHD;
   int64_t nthreads;
 };
 
@@ -45,17 +49,31 @@ template <int MODE, int DIST, int PS, bool FAST, bool KSPLIT>
 __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_bwd_kernel(const __grid_constant__ BwdParams P) {
   const stnls_geom& g = P.g;
   const stnls_search_opts& o = P.o;
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P.nthreads) return;
-  int c4, nw, nh, tl, hd;
-  int64_t wq = divmod(idx, P.nquad, c4);
-  c4 *= 4;
+  int c4, nw, nh, tl, hd, n, b;
+  int64_t wq;
   int k_lo = 0, k_hi = P.K;
-  if (KSPLIT) { wq = divmod(wq, P.K, k_lo); k_hi = k_lo + 1; }
-  int64_t r = divmod(wq, g.nW, nw);
-  r = divmod(r, g.nH, nh);
-  r = divmod(r, g.Tq, tl);
-  const int n = (int)r, b = (int)divmod(r, g.HD, hd);
+  if (P.idx32) {   // grid.x = the threads of one frame, grid.y/z = frames (common.cuh frame_grid): multiply-high divisions
+    unsigned u = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned fr = blockIdx.y + blockIdx.z * gridDim.y;
+    if (u >= P.per_frame || fr >= P.frames) return;
+    u = fdivmod(u, P.fquad, c4);
+    if (KSPLIT) { u = fdivmod(u, P.fK, k_lo); k_hi = k_lo + 1; }
+    nh = (int)fdivmod(u, P.fnW, nw);
+    n = (int)fdivmod(fr, P.fTq, tl);
+    b = (int)fdivmod((unsigned)n, P.fHD, hd);
+    wq = ((int64_t)fr * g.nH + nh) * g.nW + nw;
+  } else {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.nthreads) return;
+    wq = divmod(idx, P.nquad, c4);
+    if (KSPLIT) { wq = divmod(wq, P.K, k_lo); k_hi = k_lo + 1; }
+    int64_t r = divmod(wq, g.nW, nw);
+    r = divmod(r, g.nH, nh);
+    r = divmod(r, g.Tq, tl);
+    n = (int)r;
+    b = (int)divmod(r, g.HD, hd);
+  }
+  c4 *= 4;
   const int t = tl + g.tq0;
   const int ah = (nh * o.stride0) % g.kH, aw = (nw * o.stride0) % g.kW;
   const int rh = (MODE == 0) ? (nh * o.strideQ) % g.qH : ah;
@@ -345,7 +363,7 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
 template <int MODE, int DIST, bool KSPLIT>
 void launch_bwd_k(const BwdParams& P, cudaStream_t st) {
   const int tpb = 128;
-  unsigned blocks = (unsigned)((P.nthreads + tpb - 1) / tpb);
+  const dim3 blocks(P.gx, P.gy, P.gz);
   if (P.o.ps == 1) search_bwd_kernel<MODE, DIST, 1, false, KSPLIT><<<blocks, tpb, 0, st>>>(P);
   else if (P.o.ps == 3 && P.fast3 && MODE != 0) search_bwd_kernel<MODE, DIST, 3, true, KSPLIT><<<blocks, tpb, 0, st>>>(P);
   else if (P.o.ps == 3) search_bwd_kernel<MODE, DIST, 3, false, KSPLIT><<<blocks, tpb, 0, st>>>(P);
@@ -393,6 +411,16 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   if (env_ks) P.ksplit = (env_ks[0] == '1' && P.mode != 0) ? 1 : 0;
   if (P.ksplit) P.nthreads *= K;
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "search_backward: too many threads for one launch");
+  {
+    const int64_t per_frame = (int64_t)g->nH * g->nW * P.nquad * (P.ksplit ? K : 1), frames = (int64_t)g->B * g->HD * g->Tq;
+    dim3 grid;
+    P.idx32 = (!getenv("STNLS_NO_FRAMEGRID") && frame_grid(per_frame, frames, 128, grid)) ? 1 : 0;
+    if (!P.idx32) grid = dim3((unsigned)((P.nthreads + 127) / 128));
+    P.gx = grid.x; P.gy = grid.y; P.gz = grid.z;
+    P.per_frame = (unsigned)per_frame; P.frames = (unsigned)frames;
+    P.fquad = make_fastdiv(P.nquad); P.fK = make_fastdiv(K); P.fnW = make_fastdiv(g->nW);
+    P.fTq = make_fastdiv(g->Tq); P.fHD = make_fastdiv(g->HD);
+  }
   cudaStream_t st = (cudaStream_t)stream;
   switch (P.mode * 2 + (o->dist_type ? 1 : 0)) {
     case 0: launch_bwd<0, 0>(P, st); break;

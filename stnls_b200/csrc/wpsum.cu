@@ -30,6 +30,9 @@ struct AggParams {
   int nquad;
   int stack;         // 1: NonLocalGather -- no sum over K, slab (n*K + k) of out / gout belongs to neighbour k
   int qagg;          // backward: channel quads are a power of two -> per-pair sums are reduced across the quad lanes
+  int idx32;         // backward: launch shape of frame_grid() (common.cuh), thread index decoded with the FastDivs
+  unsigned per_frame, frames;
+  FastDiv fquad, fK, fnW, fTq;
   int64_t nthreads;
 };
 
@@ -291,17 +294,29 @@ __global__ void __launch_bounds__(128, WB_MINB) wpsum_bwd_kernel(const __grid_co
   const stnls_geom& g = P.g;
   const stnls_agg_opts& o = P.o;
   const int H = g.kH, W = g.kW;
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P.nthreads) return;
-  int c4, nw, nh, tl;
-  int64_t wq = divmod(idx, P.nquad, c4);
-  c4 *= 4;
+  int c4, nw, nh, tl, n;
+  int64_t wq;
   int k_lo = 0, k_hi = o.K;
-  if (KSPLIT) { wq = divmod(wq, o.K, k_lo); k_hi = k_lo + 1; }
-  int64_t r = divmod(wq, g.nW, nw);
-  r = divmod(r, g.nH, nh);
-  r = divmod(r, g.Tq, tl);
-  const int n = (int)r;
+  if (P.idx32) {
+    unsigned u = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned fr = blockIdx.y + blockIdx.z * gridDim.y;
+    if (u >= P.per_frame || fr >= P.frames) return;
+    u = fdivmod(u, P.fquad, c4);
+    if (KSPLIT) { u = fdivmod(u, P.fK, k_lo); k_hi = k_lo + 1; }
+    nh = (int)fdivmod(u, P.fnW, nw);
+    n = (int)fdivmod(fr, P.fTq, tl);
+    wq = ((int64_t)fr * g.nH + nh) * g.nW + nw;
+  } else {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.nthreads) return;
+    wq = divmod(idx, P.nquad, c4);
+    if (KSPLIT) { wq = divmod(wq, o.K, k_lo); k_hi = k_lo + 1; }
+    int64_t r = divmod(wq, g.nW, nw);
+    r = divmod(r, g.nH, nh);
+    r = divmod(r, g.Tq, tl);
+    n = (int)r;
+  }
+  c4 *= 4;
   const int t = tl + g.tq0;
   const int rh = (nh * o.stride0) % H, rw = (nw * o.stride0) % W;
   const int64_t vfs = (int64_t)H * W * g.Fp;
@@ -590,15 +605,23 @@ static int agg_backward(float* gv_cl, float* grad_weights, float* grad_flows, co
     STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_backward: too many threads for one launch");
     blocks = (unsigned)((P.nthreads + 127) / 128);
   }
+  dim3 grid(blocks);
+  {
+    const int64_t per_frame = (int64_t)g->nH * g->nW * P.nquad * (ksplit ? o->K : 1), frames = (int64_t)g->B * g->HD * g->Tq;
+    P.idx32 = (!getenv("STNLS_NO_FRAMEGRID") && frame_grid(per_frame, frames, 128, grid)) ? 1 : 0;
+    if (!P.idx32) grid = dim3(blocks);
+    P.per_frame = (unsigned)per_frame; P.frames = (unsigned)frames;
+    P.fquad = make_fastdiv(P.nquad); P.fK = make_fastdiv(o->K); P.fnW = make_fastdiv(g->nW); P.fTq = make_fastdiv(g->Tq);
+  }
   if (o->itype_int) {
-    if (ksplit) wpsum_bwd_kernel<true, false, true><<<blocks, 128, 0, st>>>(P);
-    else wpsum_bwd_kernel<true, false, false><<<blocks, 128, 0, st>>>(P);
+    if (ksplit) wpsum_bwd_kernel<true, false, true><<<grid, 128, 0, st>>>(P);
+    else wpsum_bwd_kernel<true, false, false><<<grid, 128, 0, st>>>(P);
   } else if (fast3) {
-    if (ksplit) wpsum_bwd_kernel<false, true, true><<<blocks, 128, 0, st>>>(P);
-    else wpsum_bwd_kernel<false, true, false><<<blocks, 128, 0, st>>>(P);
+    if (ksplit) wpsum_bwd_kernel<false, true, true><<<grid, 128, 0, st>>>(P);
+    else wpsum_bwd_kernel<false, true, false><<<grid, 128, 0, st>>>(P);
   } else {
-    if (ksplit) wpsum_bwd_kernel<false, false, true><<<blocks, 128, 0, st>>>(P);
-    else wpsum_bwd_kernel<false, false, false><<<blocks, 128, 0, st>>>(P);
+    if (ksplit) wpsum_bwd_kernel<false, false, true><<<grid, 128, 0, st>>>(P);
+    else wpsum_bwd_kernel<false, false, false><<<grid, 128, 0, st>>>(P);
   }
   STNLS_CHECK_LAUNCH("wpsum_backward");
   return STNLS_OK;
