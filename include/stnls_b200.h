@@ -82,6 +82,18 @@ int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, int t0, int 
                     int H, int W, int64_t sB, int64_t sHD, int64_t sT, int64_t sC,
                     int accumulate, stnls_stream_t stream);
 
+/* several videos in ONE launch (q, k, v of a step; the three gradients on the way back): the per-video arguments of
+ * stnls_pack_cl / stnls_unpack_cl as HOST arrays of njobs <= 4 entries; strides holds (sB, sHD, sT, sC) per video;
+ * Fp = F rounded up to 4; counts_h / counts_w / accumulate may be NULL (no division / overwrite).  Same copy as
+ * shape_vids (lib/stnls/search/utils.py:178-190) for all inputs of a search + aggregation step at once.              */
+int stnls_pack_cl_multi(int njobs, float* const* dst_cl, const float* const* src, const int* B, const int* HD,
+                        const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
+                        const int64_t* strides, const int* const* counts_h, const int* const* counts_w,
+                        stnls_stream_t stream);
+int stnls_unpack_cl_multi(int njobs, float* const* dst, const float* const* src_cl, const int* B, const int* HD,
+                          const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
+                          const int64_t* strides, const int* accumulate, stnls_stream_t stream);
+
 /* ---- search forward: kernel + anchor_self + top-K fused ------------------------------------
  * replaces  stnls_cuda.non_local_search_{int,bilin2d}_forward + stnls_cuda.anchor_self + stnls.nn.topk
  *           (impl/non_local_search.py:57-126) and
@@ -111,6 +123,17 @@ int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flows,
                           const int* kselect, const uint8_t* reflect, int K,
                           const stnls_geom* g, const stnls_search_opts* o, stnls_stream_t stream);
 
+/* search backward with the normalise step's backward folded in (SoftmaxNormalize, lib/stnls/normz/softmax.py:21-42,
+ * between the search and the aggregation): instead of grad_dists the kernel takes the gradient of the weights and the
+ * weights (B,HD,Tq,nH,nW,K) and uses grad_dists[k] = scale * w[k] * (gw[k] - sum_j w[j] gw[j]) -- the arithmetic of
+ * stnls_softmax_backward, bit for bit.  Everything else as stnls_search_backward.                                  */
+int stnls_search_backward_sm(float* gq_cl, float* gk_cl, float* grad_flows,
+                             const float* q_cl, const float* k_cl, const float* flows,
+                             const float* grad_weights, const float* weights, float scale,
+                             const float* grad_inds, const void* inds,
+                             const int* kselect, const uint8_t* reflect, int K,
+                             const stnls_geom* g, const stnls_search_opts* o, stnls_stream_t stream);
+
 /* ---- weighted patch sum (== NonLocalGatherAdd) ------------------------------------------------
  * replaces  gather_add_forward / gather_add_int_backward / gather_add_bilin2d_backward
  *           (lib/csrc/agg/gather_add.cpp:53-57,68-73,86-92)
@@ -125,6 +148,14 @@ typedef struct {
 int stnls_wpsum_forward(float* out_cl, const float* v_cl, const float* weights, const void* flows,
                         const int* counts_h, const int* counts_w,
                         const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream);
+/* the same with the normalise step folded in: weights = softmax(scale * dists[..., :K]) is computed
+ * inside the aggregation kernel -- the arithmetic of stnls_softmax_forward, bit for bit -- and WRITTEN to `weights`
+ * (B,HD,Tq,nH,nW,K) for the backward pass; rows of dists hold Kin >= K entries.  *launches (may be NULL) = kernels
+ * run: 1, or 2 where the fused kernel does not apply (ps != 3, dilation != 1, more than 32 channels per head) and
+ * the normalise kernel runs first.                                                                               */
+int stnls_wpsum_forward_sm(float* out_cl, float* weights, const float* v_cl, const float* dists, int Kin, float scale,
+                           const void* flows, const int* counts_h, const int* counts_w,
+                           const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream, int* launches);
 /*  gout_cl (N,Tq,H,W,Fp): incoming gradient already divided by counts (stnls_pack_cl does it)
  *  gv_cl (N,Tk,H,W,Fp) pre-zeroed; grad_weights (B,HD,Tq,nH,nW,K) pre-zeroed;
  *  grad_flows (…,K,3) pre-zeroed or NULL (int)                                                  */

@@ -65,6 +65,67 @@ __global__ void __launch_bounds__(256) layout_kernel(const __grid_constant__ Lay
   }
 }
 
+// Several videos in ONE launch (q, k, v of a step; the three gradients on the way back): blockIdx.z walks the slabs of
+// all jobs, a block whose (x, y) lies outside a smaller job's frame skips it.  Same per-slab body as layout_kernel.
+constexpr int LAYOUT_MAX_JOBS = 4;
+struct LayoutJobs {
+  LayoutParams job[LAYOUT_MAX_JOBS];
+  int64_t zend[LAYOUT_MAX_JOBS];   // cumulative slab counts
+  int njobs;
+};
+
+template <bool PACK>
+__global__ void __launch_bounds__(256) layout_multi_kernel(const __grid_constant__ LayoutJobs J) {
+  extern __shared__ float tile[];  // [max Fp][33]
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int w0 = blockIdx.x * 32, h = blockIdx.y;
+  const int64_t total = J.zend[J.njobs - 1];
+  for (int64_t zz = blockIdx.z; zz < total; zz += gridDim.z) {
+    int j = 0;
+    while (zz >= J.zend[j]) j++;
+    const LayoutParams& P = J.job[j];
+    if (w0 >= P.W || h >= P.H) continue;   // block-uniform
+    const int64_t z = zz - (j ? J.zend[j - 1] : 0);
+    const int tl = (int)(z % P.Tloc), n = (int)(z / P.Tloc);
+    const int b = n / P.HD, hd = n % P.HD;
+    float* pl = P.planar + (int64_t)b * P.sB + (int64_t)hd * P.sHD + (int64_t)(P.t0 + tl) * P.sT + (int64_t)h * P.W;
+    float* cl = P.cl + ((((int64_t)n * P.Tloc + tl) * P.H + h) * P.W + w0) * P.Fp;
+    const int wn = min(32, P.W - w0);
+    if (PACK) {
+      float inv = 1.f;
+      const bool div = P.counts_h != nullptr;
+      if (div && tx < wn) inv = (float)(P.counts_h[h] * P.counts_w[w0 + tx]);
+      for (int c = ty; c < P.Fp; c += 8) {
+        float v = 0.f;
+        if (c < P.F && tx < wn) {
+          v = pl[(int64_t)c * P.sC + w0 + tx];
+          if (div) v = v / inv;
+        }
+        tile[c * 33 + tx] = v;
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
+        int wl = i / P.Fp, c = i - wl * P.Fp;
+        cl[i] = tile[c * 33 + wl];
+      }
+    } else {
+      for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
+        int wl = i / P.Fp, c = i - wl * P.Fp;
+        tile[c * 33 + wl] = cl[i];
+      }
+      __syncthreads();
+      for (int c = ty; c < P.F; c += 8) {
+        if (tx < wn) {
+          float* d = pl + (int64_t)c * P.sC + w0 + tx;
+          float v = tile[c * 33 + tx];
+          *d = P.accumulate ? (*d + v) : v;
+        }
+      }
+    }
+    __syncthreads();   // the tile is reused by the next slab
+  }
+}
+
 __global__ void add_inplace_kernel(float* dst, const float* src, int64_t n) {
   int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i + 3 < n) {
@@ -145,6 +206,58 @@ extern "C" int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, i
   P.H = H; P.W = W; P.sB = sB; P.sHD = sHD; P.sT = sT; P.sC = sC; P.counts_h = nullptr; P.counts_w = nullptr;
   P.accumulate = accumulate;
   return launch_layout(false, P, B, (cudaStream_t)stream, "unpack_cl");
+}
+
+// host side of the multi-job launch; job arrays are HOST arrays of njobs entries, strides 4 per job (sB,sHD,sT,sC)
+static int launch_layout_multi(bool pack, int njobs, float* const* cl, float* const* planar, const int* B, const int* HD,
+                               const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
+                               const int64_t* strides, const int* const* counts_h, const int* const* counts_w,
+                               const int* accumulate, cudaStream_t st, const char* who) {
+  STNLS_REQUIRE(njobs >= 1 && njobs <= LAYOUT_MAX_JOBS, "%s: 1..%d videos per launch", who, LAYOUT_MAX_JOBS);
+  STNLS_REQUIRE(cl && planar && B && HD && t0 && Tloc && F && H && W && strides, "%s: null argument", who);
+  LayoutJobs J;
+  int64_t z = 0;
+  int maxW = 0, maxH = 0, maxFp = 0;
+  for (int j = 0; j < njobs; j++) {
+    LayoutParams& P = J.job[j];
+    STNLS_REQUIRE(cl[j] && planar[j], "%s: null video %d", who, j);
+    P.cl = cl[j]; P.planar = planar[j]; P.HD = HD[j]; P.t0 = t0[j]; P.Tloc = Tloc[j]; P.F = F[j]; P.Fp = (F[j] + 3) / 4 * 4;
+    P.H = H[j]; P.W = W[j]; P.sB = strides[4 * j]; P.sHD = strides[4 * j + 1]; P.sT = strides[4 * j + 2]; P.sC = strides[4 * j + 3];
+    P.counts_h = counts_h ? counts_h[j] : nullptr; P.counts_w = counts_w ? counts_w[j] : nullptr;
+    STNLS_REQUIRE((P.counts_h == nullptr) == (P.counts_w == nullptr), "%s: counts_h and counts_w go together", who);
+    P.accumulate = accumulate ? accumulate[j] : 0;
+    STNLS_REQUIRE(P.F > 0 && P.HD > 0 && B[j] >= 0 && P.Tloc >= 0 && P.H >= 0 && P.W >= 0, "%s: bad shape of video %d", who, j);
+    STNLS_REQUIRE(P.H <= 65535, "%s: H too large", who);
+    P.nz = (int64_t)B[j] * P.HD * P.Tloc;
+    if (P.H == 0 || P.W == 0) P.nz = 0;
+    z += P.nz;
+    J.zend[j] = z;
+    maxW = P.W > maxW ? P.W : maxW; maxH = P.H > maxH ? P.H : maxH; maxFp = P.Fp > maxFp ? P.Fp : maxFp;
+  }
+  J.njobs = njobs;
+  if (z == 0) return STNLS_OK;
+  const size_t smem = (size_t)maxFp * 33 * sizeof(float);
+  STNLS_REQUIRE(smem <= 48 * 1024, "%s: more than 372 channels per head: use the single-video call", who);
+  dim3 grid((maxW + 31) / 32, maxH, (unsigned)(z < 65535 ? z : 65535));
+  if (pack) layout_multi_kernel<true><<<grid, 256, smem, st>>>(J);
+  else layout_multi_kernel<false><<<grid, 256, smem, st>>>(J);
+  STNLS_CHECK_LAUNCH(who);
+  return STNLS_OK;
+}
+
+extern "C" int stnls_pack_cl_multi(int njobs, float* const* dst_cl, const float* const* src, const int* B, const int* HD,
+                                   const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
+                                   const int64_t* strides, const int* const* counts_h, const int* const* counts_w,
+                                   stnls_stream_t stream) {
+  return launch_layout_multi(true, njobs, dst_cl, const_cast<float* const*>(src), B, HD, t0, Tloc, F, H, W, strides,
+                             counts_h, counts_w, nullptr, (cudaStream_t)stream, "pack_cl_multi");
+}
+
+extern "C" int stnls_unpack_cl_multi(int njobs, float* const* dst, const float* const* src_cl, const int* B, const int* HD,
+                                     const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
+                                     const int64_t* strides, const int* accumulate, stnls_stream_t stream) {
+  return launch_layout_multi(false, njobs, const_cast<float* const*>(src_cl), dst, B, HD, t0, Tloc, F, H, W, strides,
+                             nullptr, nullptr, accumulate, (cudaStream_t)stream, "unpack_cl_multi");
 }
 
 extern "C" int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t stream) {

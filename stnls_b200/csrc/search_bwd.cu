@@ -28,6 +28,9 @@ struct BwdParams {
   const float* k;
   const float* flows;
   const float* gd;
+  const float* gw;       // fused normalise backward: grad_dists is not read, it is computed from the
+  const float* w;        //   gradient of the weights and the weights: gd[k] = sm_scale * w[k] * (gw[k] - sum_j w[j] gw[j])
+  float sm_scale;
   const float* gi;
   const void* inds;
   const int* kselect;
@@ -95,10 +98,24 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
 #pragma unroll
   for (int i = 0; i < (ACCQ ? PS * PS : 1); i++) acc[i] = f4zero();
 
+  // grad_dists of neighbour oi: read, or (fused normalise backward) the arithmetic of softmax_bwd_kernel (normz.cu) in
+  // the same order, so both routes give the same bits
+  const bool smb = P.gw != nullptr;
+  float sm_dot = 0.f;
+  if (smb) {
+    const float* wr = P.w + wq * P.K;
+    const float* gr = P.gw + wq * P.K;
+    for (int j = 0; j < P.K; j++) sm_dot = fmaf(__ldg(wr + j), __ldg(gr + j), sm_dot);
+  }
+  auto gdist = [&](int64_t oi) -> float {
+    if (!smb) return P.gd[oi];
+    return __fmul_rn(__fmul_rn(P.sm_scale, __ldg(P.w + oi)), __fsub_rn(__ldg(P.gw + oi), sm_dot));
+  };
+
   if (MODE == 0) {  // nls_int.cu:88-167
     for (int ki = k_lo; ki < k_hi; ki++) {
       const int64_t oi = wq * P.K + ki;
-      const float weight = P.gd[oi];
+      const float weight = gdist(oi);
       const int* ind = reinterpret_cast<const int*>(P.inds) + oi * 3;
       const int p0 = bnd(t + ind[0], g.T);
       const int ph = ah + ind[1], pw = aw + ind[2];
@@ -143,7 +160,7 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
     auto preamble = [&](int ki, bool first) {
       Pre z;
       const int64_t oi = wq * P.K + ki;
-      z.weight = P.gd[oi];
+      z.weight = gdist(oi);
       const float* ind = reinterpret_cast<const float*>(P.inds) + oi * 3;
       z.pp0 = (float)t + ind[0]; z.pph = (float)ah + ind[1]; z.ppw = (float)aw + ind[2];
       z.iw0 = z.iw1 = 0.f;
@@ -377,18 +394,20 @@ void launch_bwd(const BwdParams& P, cudaStream_t st) {
 
 }  // namespace
 
-extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flows, const float* q_cl,
-                                     const float* k_cl, const float* flows, const float* grad_dists,
-                                     const float* grad_inds, const void* inds, const int* kselect,
-                                     const uint8_t* reflect, int K, const stnls_geom* g,
-                                     const stnls_search_opts* o, stnls_stream_t stream) {
-  STNLS_REQUIRE(gq_cl && gk_cl && q_cl && k_cl && grad_dists && inds && g && o, "search_backward: null argument");
+static int search_backward_impl(float* gq_cl, float* gk_cl, float* grad_flows, const float* q_cl,
+                                const float* k_cl, const float* flows, const float* grad_dists,
+                                const float* grad_inds, const void* inds, const int* kselect,
+                                const uint8_t* reflect, int K, const stnls_geom* g,
+                                const stnls_search_opts* o, stnls_stream_t stream, const float* grad_weights,
+                                const float* weights, float sm_scale) {
+  STNLS_REQUIRE(gq_cl && gk_cl && q_cl && k_cl && (grad_dists || (grad_weights && weights)) && inds && g && o,
+                "search_backward: null argument");
   STNLS_REQUIRE(g->Fp % 4 == 0, "search_backward: Fp must be a multiple of 4");
   STNLS_REQUIRE(o->dist_type == 0 || o->dist_type == 1, "Uknown distance type. Must be 0 (product) or 1 (l2)");
   if (int rc = stnls_check_geom(g, -1, "search_backward")) return rc;
   BwdParams P;
   P.gq = gq_cl; P.gk = gk_cl; P.gflows = grad_flows; P.q = q_cl; P.k = k_cl; P.flows = flows;
-  P.gd = grad_dists; P.gi = grad_inds; P.inds = inds; P.kselect = kselect; P.reflect = reflect;
+  P.gd = grad_dists; P.gw = grad_dists ? nullptr : grad_weights; P.w = weights; P.sm_scale = sm_scale; P.gi = grad_inds; P.inds = inds; P.kselect = kselect; P.reflect = reflect;
   P.g = *g; P.o = *o; P.K = K; P.nquad = g->Fp / 4; P.W_t = 2 * o->wt + 1;
   P.fast3 = (o->ps == 3 && o->dilation == 1 && !getenv("STNLS_NO_FAST3")) ? 1 : 0;
   const bool refine = o->wr > 0;
@@ -434,4 +453,24 @@ extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flo
   }
   STNLS_CHECK_LAUNCH("search_backward");
   return STNLS_OK;
+}
+
+extern "C" int stnls_search_backward(float* gq_cl, float* gk_cl, float* grad_flows, const float* q_cl,
+                                     const float* k_cl, const float* flows, const float* grad_dists,
+                                     const float* grad_inds, const void* inds, const int* kselect,
+                                     const uint8_t* reflect, int K, const stnls_geom* g,
+                                     const stnls_search_opts* o, stnls_stream_t stream) {
+  STNLS_REQUIRE(grad_dists, "search_backward: null argument");
+  return search_backward_impl(gq_cl, gk_cl, grad_flows, q_cl, k_cl, flows, grad_dists, grad_inds, inds, kselect, reflect, K,
+                              g, o, stream, nullptr, nullptr, 0.f);
+}
+
+extern "C" int stnls_search_backward_sm(float* gq_cl, float* gk_cl, float* grad_flows, const float* q_cl,
+                                        const float* k_cl, const float* flows, const float* grad_weights,
+                                        const float* weights, float scale, const float* grad_inds, const void* inds,
+                                        const int* kselect, const uint8_t* reflect, int K, const stnls_geom* g,
+                                        const stnls_search_opts* o, stnls_stream_t stream) {
+  STNLS_REQUIRE(grad_weights && weights, "search_backward_sm: null argument");
+  return search_backward_impl(gq_cl, gk_cl, grad_flows, q_cl, k_cl, flows, nullptr, grad_inds, inds, kselect, reflect, K, g, o,
+                              stream, grad_weights, weights, scale);
 }

@@ -30,6 +30,10 @@ struct AggParams {
   int nquad;
   int stack;         // 1: NonLocalGather -- no sum over K, slab (n*K + k) of out / gout belongs to neighbour k
   int qagg;          // backward: channel quads are a power of two -> per-pair sums are reduced across the quad lanes
+  const float* dists;   // forward, fused normalise step: weights = softmax(sm_scale * dists[row, :K]) computed in the
+  float* weights_out;   //   kernel (and written here for the backward); rows of dists have Kin >= K entries
+  float sm_scale;
+  int Kin;
   int idx32;         // backward: launch shape of frame_grid() (common.cuh), thread index decoded with the FastDivs
   unsigned per_frame, frames;
   FastDiv fquad, fK, fnW, fTq;
@@ -169,15 +173,33 @@ __global__ void __launch_bounds__(512) wpsum_fwd_tile_kernel(const __grid_consta
         }
       }
     };
+    // fused normalise step: the query's softmax statistics, the same arithmetic in the same order as
+    // softmax_fwd_kernel (normz.cu) so that both routes give the same bits; the tile that holds the query's reference
+    // pixel writes the weights for the backward pass
+    const bool sm = P.dists != nullptr;
+    const float* drow = sm ? P.dists + (qb / o.K) * P.Kin : nullptr;
+    float sm_m = 0.f, sm_inv = 0.f;
+    if (sm) {
+      float m = -INFINITY, ssum = 0.f;
+      for (int k = 0; k < o.K; k++) m = fmaxf(m, __fmul_rn(P.sm_scale, __ldg(drow + k)));
+      for (int k = 0; k < o.K; k++) ssum = __fadd_rn(ssum, expf(__fsub_rn(__fmul_rn(P.sm_scale, __ldg(drow + k)), m)));
+      sm_m = m; sm_inv = 1.f / ssum;
+    }
+    auto wload = [&](int ki) -> float {
+      if (!sm) return __ldg(P.weights + qb + ki);
+      return __fmul_rn(expf(__fsub_rn(__fmul_rn(P.sm_scale, __ldg(drow + ki)), sm_m)), sm_inv);
+    };
+    const bool wowner = sm && c4 == 0 && rh >= h0 && rh < h0 + C.TH && rw >= w0 && rw < w0 + C.TW;
     // the (weight, offset) of neighbour k+1 is fetched while neighbour k is processed
     const int* fi = reinterpret_cast<const int*>(P.flows) + qb * 3;
-    float wnext = __ldg(P.weights + qb);
+    float wnext = wload(0);
     int x0 = __ldg(fi), x1 = __ldg(fi + 1), x2 = __ldg(fi + 2);
     for (int ki = 0; ki < o.K; ki++) {
       const float weight = wnext;
       const int y0 = x0, y1 = x1, y2 = x2;
+      if (wowner) P.weights_out[qb + ki] = weight;
       if (ki + 1 < o.K) {
-        wnext = __ldg(P.weights + qb + ki + 1);
+        wnext = wload(ki + 1);
         x0 = __ldg(fi + (ki + 1) * 3); x1 = __ldg(fi + (ki + 1) * 3 + 1); x2 = __ldg(fi + (ki + 1) * 3 + 2);
       }
       if (INT) {
@@ -250,7 +272,7 @@ __global__ void __launch_bounds__(512) wpsum_fwd_tile_kernel(const __grid_consta
       slow &= slow - 1;
       const float* f = reinterpret_cast<const float*>(P.flows) + (qb + ki) * 3;
       float n0 = bnd((float)t + __ldg(f), g.T), c1 = bnd((float)rh + __ldg(f + 1), H), c2 = bnd((float)rw + __ldg(f + 2), W);
-      slow_path(__ldg(P.weights + qb + ki), n0, c1, c2);
+      slow_path(wload(ki), n0, c1, c2);
     }
   }
   // 9 phases: patch pixel (pi,pj) of every query lands on a different tile pixel
@@ -527,11 +549,14 @@ int agg_check(const stnls_geom* g, const stnls_agg_opts* o, const char* who) {
 
 }  // namespace
 
+// dists != NULL: fused normalise step -- `weights` is then an OUTPUT (softmax(scale * dists[:, :K])); *launches = kernels run
 static int agg_forward(float* out_cl, const float* v_cl, const float* weights, const void* flows,
                        const int* counts_h, const int* counts_w, const stnls_geom* g,
-                       const stnls_agg_opts* o, stnls_stream_t stream, int stack) {
+                       const stnls_agg_opts* o, stnls_stream_t stream, int stack, const float* dists = nullptr,
+                       int Kin = 0, float scale = 0.f, int* launches = nullptr) {
   if (int rc = agg_check(g, o, "wpsum_forward")) return rc;
   STNLS_REQUIRE(out_cl && v_cl && weights && flows && counts_h && counts_w, "wpsum_forward: null argument");
+  if (launches) *launches = 0;
   AggParams P = {};
   P.out = out_cl; P.v = v_cl; P.weights = weights; P.flows = flows; P.counts_h = counts_h; P.counts_w = counts_w;
   P.g = *g; P.o = *o; P.nquad = g->Fp / 4;
@@ -541,27 +566,37 @@ static int agg_forward(float* out_cl, const float* v_cl, const float* weights, c
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "wpsum_forward: too many threads for one launch");
   unsigned blocks = (unsigned)((P.nthreads + 127) / 128);
   cudaStream_t st = (cudaStream_t)stream;
-  if (!stack && o->ps == 3 && o->dilation == 1 && P.nquad <= 8 && !getenv("STNLS_WPF_NO_TILE")) {
-    // tile: the largest with (queries touching the tile) x quads <= 512 threads
-    static const int dims[5][2] = {{16, 32}, {16, 16}, {12, 16}, {8, 16}, {8, 8}};
-    TileCfg C = {};
-    for (int i = 0; i < 5; i++) {
-      C.TH = dims[i][0]; C.TW = dims[i][1];
-      C.nQh = (C.TH + 1) / o->stride0 + 1; C.nQw = (C.TW + 1) / o->stride0 + 1;
-      if (C.nQh * C.nQw * P.nquad <= 512) break;
+  if (launches) *launches = 1;
+  // tile kernel: the largest tile with (queries touching the tile) x quads <= 512 threads
+  static const int dims[5][2] = {{16, 32}, {16, 16}, {12, 16}, {8, 16}, {8, 8}};
+  TileCfg C = {};
+  for (int i = 0; i < 5; i++) {
+    C.TH = dims[i][0]; C.TW = dims[i][1];
+    C.nQh = (C.TH + 1) / o->stride0 + 1; C.nQw = (C.TW + 1) / o->stride0 + 1;
+    if (C.nQh * C.nQw * P.nquad <= 512) break;
+  }
+  const int threads = (C.nQh * C.nQw * P.nquad + 31) / 32 * 32;
+  const int64_t ny = (int64_t)g->B * g->HD * g->Tq;
+  const bool tile_ok = !stack && o->ps == 3 && o->dilation == 1 && P.nquad <= 8 && !getenv("STNLS_WPF_NO_TILE") &&
+                       threads <= 512 && ny <= 65535;
+  if (dists) {
+    STNLS_REQUIRE(o->K > 0 && Kin >= o->K, "wpsum_forward_sm: rows of dists must hold at least K entries (K=%d, Kin=%d)", o->K, Kin);
+    if (tile_ok && !getenv("STNLS_WPF_NO_FUSED_SM")) {
+      P.dists = dists; P.weights_out = const_cast<float*>(weights); P.sm_scale = scale; P.Kin = Kin;
+    } else {   // the gather kernel would redo the row statistics once per covered pixel: normalise first, two launches
+      if (int rc = stnls_softmax_forward(const_cast<float*>(weights), dists, ny * g->nH * g->nW, o->K, Kin, scale, stream)) return rc;
+      if (launches) *launches = 2;
     }
-    const int threads = (C.nQh * C.nQw * P.nquad + 31) / 32 * 32;
+  }
+  if (tile_ok) {
     C.tiles_w = (g->kW + C.TW - 1) / C.TW;
     const int tiles_h = (g->kH + C.TH - 1) / C.TH;
-    const int64_t ny = (int64_t)g->B * g->HD * g->Tq;
-    if (threads <= 512 && ny <= 65535) {
-      dim3 grid((unsigned)(C.tiles_w * tiles_h), (unsigned)ny);
-      const size_t smem = (size_t)C.TH * C.TW * P.nquad * 16;
-      if (o->itype_int) wpsum_fwd_tile_kernel<true><<<grid, threads, smem, st>>>(P, C);
-      else wpsum_fwd_tile_kernel<false><<<grid, threads, smem, st>>>(P, C);
-      STNLS_CHECK_LAUNCH("wpsum_forward(tile)");
-      return STNLS_OK;
-    }
+    dim3 grid((unsigned)(C.tiles_w * tiles_h), (unsigned)ny);
+    const size_t smem = (size_t)C.TH * C.TW * P.nquad * 16;
+    if (o->itype_int) wpsum_fwd_tile_kernel<true><<<grid, threads, smem, st>>>(P, C);
+    else wpsum_fwd_tile_kernel<false><<<grid, threads, smem, st>>>(P, C);
+    STNLS_CHECK_LAUNCH("wpsum_forward(tile)");
+    return STNLS_OK;
   }
   if (o->itype_int) wpsum_fwd_kernel<true><<<blocks, 128, 0, st>>>(P);
   else wpsum_fwd_kernel<false><<<blocks, 128, 0, st>>>(P);
@@ -573,6 +608,12 @@ extern "C" int stnls_wpsum_forward(float* out_cl, const float* v_cl, const float
                                    const int* counts_h, const int* counts_w, const stnls_geom* g,
                                    const stnls_agg_opts* o, stnls_stream_t stream) {
   return agg_forward(out_cl, v_cl, weights, flows, counts_h, counts_w, g, o, stream, 0);
+}
+extern "C" int stnls_wpsum_forward_sm(float* out_cl, float* weights, const float* v_cl, const float* dists, int Kin,
+                                      float scale, const void* flows, const int* counts_h, const int* counts_w,
+                                      const stnls_geom* g, const stnls_agg_opts* o, stnls_stream_t stream, int* launches) {
+  STNLS_REQUIRE(dists, "wpsum_forward_sm: null argument");
+  return agg_forward(out_cl, v_cl, weights, flows, counts_h, counts_w, g, o, stream, 0, dists, Kin, scale, launches);
 }
 extern "C" int stnls_gather_forward(float* stack_cl, const float* v_cl, const float* weights, const void* flows,
                                     const int* counts_h, const int* counts_w, const stnls_geom* g,

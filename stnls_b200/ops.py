@@ -98,6 +98,52 @@ def unpack_cl(cl, shape, nheads, t0=0, out=None, accumulate=False):
     return out
 
 
+def _arr(ctype, vals):
+    return (ctype * len(vals))(*vals)
+
+
+def pack_cl_multi(vids, nheads, outs=None):
+    """[planar video] -> [channels-last copy] in ONE launch (at most 4 videos, same head count; q, k, v of a step).
+    outs: optional preallocated destinations (e.g. views into a symmetric-memory buffer)."""
+    _need_cuda(*vids)
+    assert 1 <= len(vids) <= 4
+    info = [_planar_strides(v, nheads) for v in vids]
+    res, B_, HD_, t0_, Tl_, F_, H_, W_, st_ = [], [], [], [], [], [], [], [], []
+    for i, (vid, (B, HD, T, F, H, W), strides) in enumerate(info):
+        shape = (B * HD, T, H, W, padded_channels(F))
+        out = th.empty(shape, device=vid.device, dtype=th.float32) if outs is None else outs[i]
+        assert tuple(out.shape) == shape and out.is_contiguous() and out.dtype == th.float32
+        res.append(out)
+        B_.append(B); HD_.append(HD); t0_.append(0); Tl_.append(T); F_.append(F); H_.append(H); W_.append(W)
+        st_ += list(strides)
+    n = len(vids)
+    _launch("pack_cl", _C.lib().stnls_pack_cl_multi, n, _arr(ctypes.c_void_p, [o.data_ptr() for o in res]),
+            _arr(ctypes.c_void_p, [v.data_ptr() for v, _, _ in info]), _arr(ctypes.c_int, B_), _arr(ctypes.c_int, HD_),
+            _arr(ctypes.c_int, t0_), _arr(ctypes.c_int, Tl_), _arr(ctypes.c_int, F_), _arr(ctypes.c_int, H_),
+            _arr(ctypes.c_int, W_), _arr(ctypes.c_int64, st_), None, None, _stream())
+    return res
+
+
+def unpack_cl_multi(cls, shapes, nheads):
+    """[channels-last] -> [planar tensor of shape] in ONE launch (at most 4; the three gradients of a step)."""
+    _need_cuda(*cls)
+    assert 1 <= len(cls) <= 4 and len(cls) == len(shapes)
+    outs, B_, HD_, t0_, Tl_, F_, H_, W_, st_ = [], [], [], [], [], [], [], [], []
+    for cl, shape in zip(cls, shapes):
+        out = th.empty(shape, device=cl.device, dtype=th.float32)
+        _, (B, HD, T, F, H, W), strides = _planar_strides(out, nheads)
+        assert tuple(cl.shape) == (B * HD, T, H, W, padded_channels(F)) and cl.is_contiguous()
+        outs.append(out)
+        B_.append(B); HD_.append(HD); t0_.append(0); Tl_.append(T); F_.append(F); H_.append(H); W_.append(W)
+        st_ += list(strides)
+    n = len(cls)
+    _launch("unpack_cl", _C.lib().stnls_unpack_cl_multi, n, _arr(ctypes.c_void_p, [o.data_ptr() for o in outs]),
+            _arr(ctypes.c_void_p, [c.data_ptr() for c in cls]), _arr(ctypes.c_int, B_), _arr(ctypes.c_int, HD_),
+            _arr(ctypes.c_int, t0_), _arr(ctypes.c_int, Tl_), _arr(ctypes.c_int, F_), _arr(ctypes.c_int, H_),
+            _arr(ctypes.c_int, W_), _arr(ctypes.c_int64, st_), None, _stream())
+    return outs
+
+
 def make_geom(B, HD, T, F, qH, qW, kH, kW, stride0, tq0=0, Tq=None, tk0=0, Tk=None):
     Tq = T if Tq is None else Tq
     Tk = T if Tk is None else Tk
@@ -151,6 +197,26 @@ def search_backward(q_cl, k_cl, flows, grad_dists, grad_inds, inds, kselect, ref
     return gq, gk, gflows
 
 
+def search_backward_sm(q_cl, k_cl, flows, grad_weights, weights, scale, grad_inds, inds, geom, opts, flows_grad,
+                       gk_out=None):
+    """search_backward with the normalise step's backward folded in (grad_dists computed from grad_weights, weights).
+    gk_out: optional pre-zeroed accumulator for grad_k (e.g. a symmetric-memory buffer)."""
+    _need_cuda(q_cl, k_cl, grad_weights, weights, inds)
+    K = weights.shape[-1]
+    assert grad_weights.is_contiguous() and weights.is_contiguous() and inds.is_contiguous()
+    gq = th.zeros_like(q_cl)
+    gk = th.zeros_like(k_cl) if gk_out is None else gk_out
+    gflows = None
+    if flows_grad:
+        gflows = th.zeros_like(flows, dtype=th.float32)
+        assert grad_inds is not None and grad_inds.is_contiguous() and grad_inds.dtype == th.float32
+    _launch("search_backward", _C.lib().stnls_search_backward_sm, _ptr(gq), _ptr(gk), _ptr(gflows), _ptr(q_cl),
+            _ptr(k_cl), _ptr(flows if flows_grad else None), _ptr(grad_weights), _ptr(weights), float(scale),
+            _ptr(grad_inds if flows_grad else None), _ptr(inds), None, None, K, ctypes.byref(geom), ctypes.byref(opts),
+            _stream())
+    return gq, gk, gflows
+
+
 def anchor_self_time(dists, inds, flows, wt, stride0, qH, qW, kH, kW):
     """In place on dists (B,HD,Q,G,S) / inds (B,HD,Q,G,S,3); flows (B,HD_f,T,nflow,2,nH,nW) of inds' dtype."""
     _need_cuda(dists, inds, flows)
@@ -185,9 +251,27 @@ def wpsum_forward(v_cl, weights, flows, counts, geom, opts):
     return out
 
 
-def wpsum_backward(gout_cl, v_cl, weights, flows, geom, opts):
+def wpsum_forward_sm(v_cl, dists, scale, flows, counts, geom, opts):
+    """Aggregation with the normalise step folded in: weights = softmax(scale * dists[..., :K]) inside the kernel.
+    Returns out_cl and the weights (for the backward pass)."""
+    global LAUNCHES
+    _need_cuda(v_cl, dists, flows)
+    g = geom
+    assert dists.is_contiguous() and dists.dtype == th.float32
+    Kin = dists.shape[-1]
+    out = th.empty((g.B * g.HD, g.Tq, g.kH, g.kW, g.Fp), device=v_cl.device, dtype=th.float32)
+    weights = th.empty(tuple(dists.shape[:-1]) + (opts.K,), device=v_cl.device, dtype=th.float32)
+    n = ctypes.c_int(0)
+    _launch("wpsum_forward", _C.lib().stnls_wpsum_forward_sm, _ptr(out), _ptr(weights), _ptr(v_cl), _ptr(dists), Kin,
+            float(scale), _ptr(flows), _ptr(counts[0]), _ptr(counts[1]), ctypes.byref(g), ctypes.byref(opts), _stream(),
+            ctypes.byref(n))
+    LAUNCHES += max(n.value, 1) - 1     # 2 where the normalise kernel had to run on its own
+    return out, weights
+
+
+def wpsum_backward(gout_cl, v_cl, weights, flows, geom, opts, gv_out=None):
     _need_cuda(gout_cl, v_cl, weights, flows)
-    gv = th.zeros_like(v_cl)
+    gv = th.zeros_like(v_cl) if gv_out is None else gv_out      # gv_out: pre-zeroed accumulator
     gw = th.zeros_like(weights)
     gf = None if opts.itype_int else th.zeros(flows.shape, device=flows.device, dtype=th.float32)
     _launch("wpsum_backward", _C.lib().stnls_wpsum_backward, _ptr(gv), _ptr(gw), _ptr(gf), _ptr(gout_cl), _ptr(v_cl),

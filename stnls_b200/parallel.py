@@ -386,8 +386,14 @@ class ShardedSearchAgg(th.nn.Module):
         else:
             k_ext = halo_exchange(k, self.plan, self.group, self.peer, "k")
         assert k_ext.shape[_time_dim(k_ext)] == self.plan.fb - self.plan.fa, "k must hold the owned frames + halo"
-        dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
         sign = -1.0 if self.search.dist_type == "l2" else 1.0
+        if joint or self.plan.world == 1:
+            from . import fused
+            if v_ready is None and fused.fusable(self.search, self.agg, q, k_ext, v if self.plan.world == 1 else v_ext, flows):
+                # one autograd node, 8 launches per forward + backward instead of 14 (stnls_b200/fused.py)
+                return fused.fused_search_agg(self.search, self.agg, q, k_ext, v if self.plan.world == 1 else v_ext,
+                                              flows, sign * self.scale, shard=self.plan.shard)
+        dists, inds = self.search(q, k_ext, flows, shard=self.plan.shard)
         weights = softmax_scaled(dists, sign * self.scale)   # fused sign/scale/softmax (normz)
         if v_ready is not None:
             th.cuda.current_stream().wait_event(v_ready)
