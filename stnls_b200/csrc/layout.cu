@@ -18,55 +18,12 @@ struct LayoutParams {
   int64_t nz;   // B*HD*Tloc slabs
 };
 
-// grid (ceil(W/32), H, N*Tloc), block 256, dynamic smem Fp*33 floats
-template <bool PACK>
-__global__ void __launch_bounds__(256) layout_kernel(const __grid_constant__ LayoutParams P) {
-  extern __shared__ float tile[];  // [Fp][33]
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int w0 = blockIdx.x * 32, h = blockIdx.y;
-  for (int64_t z = blockIdx.z; z < P.nz; z += gridDim.z) {   // slabs beyond the 65535 a grid's z extent can hold
-  const int tl = (int)(z % P.Tloc), n = (int)(z / P.Tloc);
-  const int b = n / P.HD, hd = n % P.HD;
-  float* pl = P.planar + (int64_t)b * P.sB + (int64_t)hd * P.sHD + (int64_t)(P.t0 + tl) * P.sT + (int64_t)h * P.W;
-  float* cl = P.cl + ((((int64_t)n * P.Tloc + tl) * P.H + h) * P.W + w0) * P.Fp;
-  const int wn = min(32, P.W - w0);
-  if (PACK) {
-    float inv = 1.f;
-    const bool div = P.counts_h != nullptr;
-    if (div && tx < wn) inv = (float)(P.counts_h[h] * P.counts_w[w0 + tx]);
-    for (int c = ty; c < P.Fp; c += 8) {
-      float v = 0.f;
-      if (c < P.F && tx < wn) {
-        v = pl[(int64_t)c * P.sC + w0 + tx];
-        if (div) v = v / inv;
-      }
-      tile[c * 33 + tx] = v;
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
-      int wl = i / P.Fp, c = i - wl * P.Fp;
-      cl[i] = tile[c * 33 + wl];
-    }
-  } else {
-    for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
-      int wl = i / P.Fp, c = i - wl * P.Fp;
-      tile[c * 33 + wl] = cl[i];
-    }
-    __syncthreads();
-    for (int c = ty; c < P.F; c += 8) {
-      if (tx < wn) {
-        float* d = pl + (int64_t)c * P.sC + w0 + tx;
-        float v = tile[c * 33 + tx];
-        *d = P.accumulate ? (*d + v) : v;
-      }
-    }
-  }
-  __syncthreads();   // the tile is reused by the next slab
-  }
-}
-
-// Several videos in ONE launch (q, k, v of a step; the three gradients on the way back): blockIdx.z walks the slabs of
-// all jobs, a block whose (x, y) lies outside a smaller job's frame skips it.  Same per-slab body as layout_kernel.
+// Several videos in ONE launch (q, k, v of a step; the three gradients on the way back), or one: blockIdx.z walks the
+// slabs (b, head, frame) of all jobs; a block whose (x, y) lies outside a smaller job's frame skips it.
+// A block moves a strip of 32 pixels x R rows x Fp channels through a padded shared tile [R][Fp][33]: on the planar side
+// every warp reads / writes 32 consecutive pixels of one channel and keeps R rows in flight per thread, on the
+// channels-last side the strip's rows are contiguous runs of 32*Fp floats moved as float4.  (Round 1 moved ONE row per
+// block -- 1 KB at 8 channels -- and ran at 0.55 TB/s on the README shape: block scheduling, not bandwidth.)
 constexpr int LAYOUT_MAX_JOBS = 4;
 struct LayoutJobs {
   LayoutParams job[LAYOUT_MAX_JOBS];
@@ -74,51 +31,64 @@ struct LayoutJobs {
   int njobs;
 };
 
-template <bool PACK>
-__global__ void __launch_bounds__(256) layout_multi_kernel(const __grid_constant__ LayoutJobs J) {
-  extern __shared__ float tile[];  // [max Fp][33]
+template <bool PACK, int R>
+__global__ void __launch_bounds__(256) layout_kernel(const __grid_constant__ LayoutJobs J) {
+  extern __shared__ __align__(16) float tile[];  // [R][max Fp][33]
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int w0 = blockIdx.x * 32, h = blockIdx.y;
+  const int w0 = blockIdx.x * 32, h0 = blockIdx.y * R;
   const int64_t total = J.zend[J.njobs - 1];
   for (int64_t zz = blockIdx.z; zz < total; zz += gridDim.z) {
     int j = 0;
     while (zz >= J.zend[j]) j++;
     const LayoutParams& P = J.job[j];
-    if (w0 >= P.W || h >= P.H) continue;   // block-uniform
+    if (w0 >= P.W || h0 >= P.H) continue;   // block-uniform
     const int64_t z = zz - (j ? J.zend[j - 1] : 0);
     const int tl = (int)(z % P.Tloc), n = (int)(z / P.Tloc);
     const int b = n / P.HD, hd = n % P.HD;
-    float* pl = P.planar + (int64_t)b * P.sB + (int64_t)hd * P.sHD + (int64_t)(P.t0 + tl) * P.sT + (int64_t)h * P.W;
-    float* cl = P.cl + ((((int64_t)n * P.Tloc + tl) * P.H + h) * P.W + w0) * P.Fp;
-    const int wn = min(32, P.W - w0);
+    const int Fp = P.Fp;
+    float* pl = P.planar + (int64_t)b * P.sB + (int64_t)hd * P.sHD + (int64_t)(P.t0 + tl) * P.sT + (int64_t)h0 * P.W + w0 + tx;
+    float* cl = P.cl + ((((int64_t)n * P.Tloc + tl) * P.H + h0) * P.W + w0) * Fp;
+    const int wn = min(32, P.W - w0), hr = min(R, P.H - h0);
+    const int per = wn * (Fp >> 2);          // float4s of one strip row on the channels-last side
+    const int64_t clrow = (int64_t)P.W * Fp;
     if (PACK) {
-      float inv = 1.f;
       const bool div = P.counts_h != nullptr;
-      if (div && tx < wn) inv = (float)(P.counts_h[h] * P.counts_w[w0 + tx]);
-      for (int c = ty; c < P.Fp; c += 8) {
-        float v = 0.f;
-        if (c < P.F && tx < wn) {
-          v = pl[(int64_t)c * P.sC + w0 + tx];
-          if (div) v = v / inv;
-        }
-        tile[c * 33 + tx] = v;
+      float inv[R];
+#pragma unroll
+      for (int r = 0; r < R; r++)
+        inv[r] = (div && r < hr && tx < wn) ? (float)(P.counts_h[h0 + r] * P.counts_w[w0 + tx]) : 1.f;
+      for (int c = ty; c < Fp; c += 8) {
+        float v[R];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+          v[r] = (c < P.F && r < hr && tx < wn) ? __ldg(pl + (int64_t)c * P.sC + (int64_t)r * P.W) : 0.f;
+#pragma unroll
+        for (int r = 0; r < R; r++) tile[(r * Fp + c) * 33 + tx] = div ? v[r] / inv[r] : v[r];
       }
       __syncthreads();
-      for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
-        int wl = i / P.Fp, c = i - wl * P.Fp;
-        cl[i] = tile[c * 33 + wl];
+      for (int i = threadIdx.x; i < hr * per; i += 256) {
+        const int r = i / per, rem = i - r * per;
+        const int wl = (rem << 2) / Fp, c = (rem << 2) - wl * Fp;
+        const float* tp = tile + (r * Fp + c) * 33 + wl;
+        *reinterpret_cast<float4*>(cl + r * clrow + ((int64_t)rem << 2)) = make_float4(tp[0], tp[33], tp[66], tp[99]);
       }
     } else {
-      for (int i = threadIdx.x; i < wn * P.Fp; i += 256) {
-        int wl = i / P.Fp, c = i - wl * P.Fp;
-        tile[c * 33 + wl] = cl[i];
+      for (int i = threadIdx.x; i < hr * per; i += 256) {
+        const int r = i / per, rem = i - r * per;
+        const int wl = (rem << 2) / Fp, c = (rem << 2) - wl * Fp;
+        const float4 x = __ldg(reinterpret_cast<const float4*>(cl + r * clrow + ((int64_t)rem << 2)));
+        float* tp = tile + (r * Fp + c) * 33 + wl;
+        tp[0] = x.x; tp[33] = x.y; tp[66] = x.z; tp[99] = x.w;
       }
       __syncthreads();
       for (int c = ty; c < P.F; c += 8) {
-        if (tx < wn) {
-          float* d = pl + (int64_t)c * P.sC + w0 + tx;
-          float v = tile[c * 33 + tx];
-          *d = P.accumulate ? (*d + v) : v;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+          if (r < hr && tx < wn) {
+            float* d = pl + (int64_t)c * P.sC + (int64_t)r * P.W;
+            const float v = tile[(r * Fp + c) * 33 + tx];
+            *d = P.accumulate ? (*d + v) : v;
+          }
         }
       }
     }
@@ -164,25 +134,55 @@ __global__ void __launch_bounds__(256) seg_copy_kernel(const __grid_constant__ S
   }
 }
 
-int launch_layout(bool pack, LayoutParams& P, int B, cudaStream_t st, const char* who) {
-  STNLS_REQUIRE(P.cl && P.planar, "%s: null argument", who);
-  STNLS_REQUIRE(P.Fp % 4 == 0 && P.Fp >= P.F && P.F > 0, "%s: Fp must be a multiple of 4 and >= F", who);
-  STNLS_REQUIRE(P.H <= 65535, "%s: H too large", who);
-  int64_t nz = (int64_t)B * P.HD * P.Tloc;
-  if (nz == 0 || P.H == 0 || P.W == 0) return STNLS_OK;
-  P.nz = nz;
-  dim3 grid((P.W + 31) / 32, P.H, (unsigned)(nz < 65535 ? nz : 65535));
-  size_t smem = (size_t)P.Fp * 33 * sizeof(float);
-  STNLS_REQUIRE(smem <= 227 * 1024, "%s: too many channels per head (%d)", who, P.F);
+template <bool PACK, int R>
+int launch_layout_r(const LayoutJobs& J, dim3 grid, size_t smem, cudaStream_t st, const char* who) {
   if (smem > 48 * 1024) {   // more than 372 channels per head: opt in to the large carve-out
-    cudaError_t e = pack ? cudaFuncSetAttribute(layout_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
-                         : cudaFuncSetAttribute(layout_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(layout_kernel<PACK, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     STNLS_REQUIRE(e == cudaSuccess, "%s: cannot reserve %zu bytes of shared memory", who, smem);
   }
-  if (pack) layout_kernel<true><<<grid, 256, smem, st>>>(P);
-  else layout_kernel<false><<<grid, 256, smem, st>>>(P);
+  layout_kernel<PACK, R><<<grid, 256, smem, st>>>(J);
   STNLS_CHECK_LAUNCH(who);
   return STNLS_OK;
+}
+
+// J.job[0..njobs) filled except nz / zend; B per job
+int launch_layout_jobs(bool pack, LayoutJobs& J, const int* B, cudaStream_t st, const char* who) {
+  int64_t z = 0;
+  int maxW = 0, maxH = 0, maxFp = 0;
+  for (int j = 0; j < J.njobs; j++) {
+    LayoutParams& P = J.job[j];
+    STNLS_REQUIRE(P.cl && P.planar, "%s: null argument", who);
+    STNLS_REQUIRE(P.Fp % 4 == 0 && P.Fp >= P.F && P.F > 0, "%s: Fp must be a multiple of 4 and >= F", who);
+    STNLS_REQUIRE(P.HD > 0 && B[j] >= 0 && P.Tloc >= 0 && P.H >= 0 && P.W >= 0, "%s: bad shape", who);
+    STNLS_REQUIRE((reinterpret_cast<uintptr_t>(P.cl) & 15) == 0, "%s: the channels-last video must be 16-byte aligned", who);
+    P.nz = (P.H == 0 || P.W == 0) ? 0 : (int64_t)B[j] * P.HD * P.Tloc;
+    z += P.nz;
+    J.zend[j] = z;
+    maxW = P.W > maxW ? P.W : maxW; maxH = P.H > maxH ? P.H : maxH; maxFp = P.Fp > maxFp ? P.Fp : maxFp;
+  }
+  if (z == 0) return STNLS_OK;
+  const int R = maxFp <= 16 ? 8 : maxFp <= 32 ? 4 : maxFp <= 64 ? 2 : 1;
+  const size_t smem = (size_t)R * maxFp * 33 * sizeof(float);
+  STNLS_REQUIRE(smem <= 227 * 1024, "%s: too many channels per head (%d)", who, maxFp);
+  STNLS_REQUIRE((maxH + R - 1) / R <= 65535, "%s: H too large", who);
+  dim3 grid((maxW + 31) / 32, (maxH + R - 1) / R, (unsigned)(z < 65535 ? z : 65535));
+  if (pack) {
+    if (R == 8) return launch_layout_r<true, 8>(J, grid, smem, st, who);
+    if (R == 4) return launch_layout_r<true, 4>(J, grid, smem, st, who);
+    if (R == 2) return launch_layout_r<true, 2>(J, grid, smem, st, who);
+    return launch_layout_r<true, 1>(J, grid, smem, st, who);
+  }
+  if (R == 8) return launch_layout_r<false, 8>(J, grid, smem, st, who);
+  if (R == 4) return launch_layout_r<false, 4>(J, grid, smem, st, who);
+  if (R == 2) return launch_layout_r<false, 2>(J, grid, smem, st, who);
+  return launch_layout_r<false, 1>(J, grid, smem, st, who);
+}
+
+int launch_layout(bool pack, LayoutParams& P, int B, cudaStream_t st, const char* who) {
+  LayoutJobs J;
+  J.job[0] = P;
+  J.njobs = 1;
+  return launch_layout_jobs(pack, J, &B, st, who);
 }
 
 }  // namespace
@@ -216,33 +216,16 @@ static int launch_layout_multi(bool pack, int njobs, float* const* cl, float* co
   STNLS_REQUIRE(njobs >= 1 && njobs <= LAYOUT_MAX_JOBS, "%s: 1..%d videos per launch", who, LAYOUT_MAX_JOBS);
   STNLS_REQUIRE(cl && planar && B && HD && t0 && Tloc && F && H && W && strides, "%s: null argument", who);
   LayoutJobs J;
-  int64_t z = 0;
-  int maxW = 0, maxH = 0, maxFp = 0;
   for (int j = 0; j < njobs; j++) {
     LayoutParams& P = J.job[j];
-    STNLS_REQUIRE(cl[j] && planar[j], "%s: null video %d", who, j);
     P.cl = cl[j]; P.planar = planar[j]; P.HD = HD[j]; P.t0 = t0[j]; P.Tloc = Tloc[j]; P.F = F[j]; P.Fp = (F[j] + 3) / 4 * 4;
     P.H = H[j]; P.W = W[j]; P.sB = strides[4 * j]; P.sHD = strides[4 * j + 1]; P.sT = strides[4 * j + 2]; P.sC = strides[4 * j + 3];
     P.counts_h = counts_h ? counts_h[j] : nullptr; P.counts_w = counts_w ? counts_w[j] : nullptr;
     STNLS_REQUIRE((P.counts_h == nullptr) == (P.counts_w == nullptr), "%s: counts_h and counts_w go together", who);
     P.accumulate = accumulate ? accumulate[j] : 0;
-    STNLS_REQUIRE(P.F > 0 && P.HD > 0 && B[j] >= 0 && P.Tloc >= 0 && P.H >= 0 && P.W >= 0, "%s: bad shape of video %d", who, j);
-    STNLS_REQUIRE(P.H <= 65535, "%s: H too large", who);
-    P.nz = (int64_t)B[j] * P.HD * P.Tloc;
-    if (P.H == 0 || P.W == 0) P.nz = 0;
-    z += P.nz;
-    J.zend[j] = z;
-    maxW = P.W > maxW ? P.W : maxW; maxH = P.H > maxH ? P.H : maxH; maxFp = P.Fp > maxFp ? P.Fp : maxFp;
   }
   J.njobs = njobs;
-  if (z == 0) return STNLS_OK;
-  const size_t smem = (size_t)maxFp * 33 * sizeof(float);
-  STNLS_REQUIRE(smem <= 48 * 1024, "%s: more than 372 channels per head: use the single-video call", who);
-  dim3 grid((maxW + 31) / 32, maxH, (unsigned)(z < 65535 ? z : 65535));
-  if (pack) layout_multi_kernel<true><<<grid, 256, smem, st>>>(J);
-  else layout_multi_kernel<false><<<grid, 256, smem, st>>>(J);
-  STNLS_CHECK_LAUNCH(who);
-  return STNLS_OK;
+  return launch_layout_jobs(pack, J, B, st, who);
 }
 
 extern "C" int stnls_pack_cl_multi(int njobs, float* const* dst_cl, const float* const* src, const int* B, const int* HD,

@@ -459,8 +459,10 @@ def test_normalize_bwd(stride0, stride1, cuda, oracle):
         (d * gd.to(cuda)).sum().backward()
         grads.append((qg.grad.cpu(), kg.grad.cpu()))
     e0, e1 = oracle.normz_bwd(grads[0][0].clone(), grads[0][1].clone(), c["ps"], stride0, stride1)
-    assert_close(grads[1][0], e0, 1e-6, 1e-5, "normalize_bwd grad_q")
-    assert_close(grads[1][1], e1, 1e-6, 1e-5, "normalize_bwd grad_k")
+    # the two backward passes are separate launches accumulating with float atomics: their sums differ by rounding
+    # in the order of arrival (a few 1e-6 at gradients of magnitude ~40), hence atol 1e-5
+    assert_close(grads[1][0], e0, 1e-5, 1e-5, "normalize_bwd grad_q")
+    assert_close(grads[1][1], e1, 1e-5, 1e-5, "normalize_bwd grad_k")
     assert not th.allclose(grads[1][0], grads[0][0])
 
 
