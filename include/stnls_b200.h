@@ -89,10 +89,14 @@ int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, int t0, int 
 int stnls_pack_cl_multi(int njobs, float* const* dst_cl, const float* const* src, const int* B, const int* HD,
                         const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
                         const int64_t* strides, const int* const* counts_h, const int* const* counts_w,
-                        stnls_stream_t stream);
+                        const int* cl_tpitch, const int* cl_t0, stnls_stream_t stream);
 int stnls_unpack_cl_multi(int njobs, float* const* dst, const float* const* src_cl, const int* B, const int* HD,
                           const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
-                          const int64_t* strides, const int* accumulate, stnls_stream_t stream);
+                          const int64_t* strides, const int* accumulate, const int* cl_tpitch, const int* cl_t0,
+                          stnls_stream_t stream);
+/* cl_tpitch / cl_t0 (NULL: Tloc / 0): the channels-last video of job j holds cl_tpitch[j] frames per (b, head) and the
+ * Tloc[j] frames moved start at its frame cl_t0[j] -- a rank packs its own frames straight into the owned + halo
+ * buffer its peers read, and unpacks the owned slice of an owned + halo gradient.                                  */
 
 /* ---- search forward: kernel + anchor_self + top-K fused ------------------------------------
  * replaces  stnls_cuda.non_local_search_{int,bilin2d}_forward + stnls_cuda.anchor_self + stnls.nn.topk
@@ -223,6 +227,12 @@ int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t st
  * peer GPU mapped into this process (NVLink peer loads).  The arrays are HOST arrays of nseg entries.          */
 int stnls_seg_copy(float* const* dst, const float* const* src, const int64_t* nfloat, int nseg, int accumulate,
                    stnls_stream_t stream);
+
+/* the same with rows: segment i is rows[i] runs of nfloat[i] floats, dst_pitch[i] / src_pitch[i] floats apart (multiples
+ * of 4) -- the frames [lo, hi) of every (batch, head) slab of a channels-last video whose slabs have different lengths
+ * on the two sides (a peer's owned + halo buffer and this rank's).                                                */
+int stnls_seg_copy2d(float* const* dst, const float* const* src, const int64_t* nfloat, const int* rows,
+                     const int64_t* dst_pitch, const int64_t* src_pitch, int nseg, int accumulate, stnls_stream_t stream);
 
 /* ---- measurement aid: fp32 FMA-pipe microbenchmark (no reference counterpart) -------------------
  * `blocks` CTAs of 256 threads, each thread 16 independent FFMA chains of `iters` steps; flops per launch =

@@ -39,7 +39,7 @@ EXPORTS = ["stnls_last_error", "stnls_version", "stnls_pack_cl", "stnls_unpack_c
            "stnls_softmax_forward", "stnls_softmax_backward", "stnls_anchor_self_time",
            "stnls_overlap_counts", "stnls_add_inplace", "stnls_ffma_peak", "stnls_seg_copy",
            "stnls_search_forward_planar_noalloc", "stnls_pack_cl_multi", "stnls_unpack_cl_multi",
-           "stnls_search_backward_sm", "stnls_wpsum_forward_sm"]
+           "stnls_search_backward_sm", "stnls_wpsum_forward_sm", "stnls_seg_copy2d"]
 
 _lib = None
 
@@ -64,8 +64,9 @@ def lib():
     L.stnls_unpack_cl.argtypes = [c_vp, c_vp] + [c_int] * 8 + [c_i64] * 4 + [c_int, c_vp]
     L.stnls_search_forward.argtypes = [c_vp] * 7 + [P(Geom), P(SearchOpts), c_vp]
     L.stnls_search_forward_planar_noalloc.argtypes = [c_vp] * 5 + [P(Geom), P(SearchOpts), c_vp]
-    L.stnls_pack_cl_multi.argtypes = [c_int] + [c_vp] * 12 + [c_vp]
-    L.stnls_unpack_cl_multi.argtypes = [c_int] + [c_vp] * 11 + [c_vp]
+    L.stnls_pack_cl_multi.argtypes = [c_int] + [c_vp] * 14 + [c_vp]
+    L.stnls_unpack_cl_multi.argtypes = [c_int] + [c_vp] * 13 + [c_vp]
+    L.stnls_seg_copy2d.argtypes = [c_vp] * 6 + [c_int, c_int, c_vp]
     L.stnls_search_backward_sm.argtypes = [c_vp] * 8 + [ctypes.c_float] + [c_vp] * 4 + [c_int, P(Geom), P(SearchOpts), c_vp]
     L.stnls_wpsum_forward_sm.argtypes = [c_vp] * 4 + [c_int, ctypes.c_float] + [c_vp] * 3 + [P(Geom), P(AggOpts), c_vp, c_vp]
     L.stnls_search_backward.argtypes = [c_vp] * 11 + [c_int, P(Geom), P(SearchOpts), c_vp]

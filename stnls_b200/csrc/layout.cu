@@ -15,6 +15,8 @@ struct LayoutParams {
   const int* counts_h;
   const int* counts_w;
   int accumulate;
+  int Tpitch, tcl0;   // the channels-last video holds Tpitch frames per (b, head); the Tloc frames start at frame tcl0
+                      // (a rank packs its OWN frames straight into the owned + halo buffer its peers read)
   int64_t nz;   // B*HD*Tloc slabs
 };
 
@@ -47,7 +49,7 @@ __global__ void __launch_bounds__(256) layout_kernel(const __grid_constant__ Lay
     const int b = n / P.HD, hd = n % P.HD;
     const int Fp = P.Fp;
     float* pl = P.planar + (int64_t)b * P.sB + (int64_t)hd * P.sHD + (int64_t)(P.t0 + tl) * P.sT + (int64_t)h0 * P.W + w0 + tx;
-    float* cl = P.cl + ((((int64_t)n * P.Tloc + tl) * P.H + h0) * P.W + w0) * Fp;
+    float* cl = P.cl + ((((int64_t)n * P.Tpitch + P.tcl0 + tl) * P.H + h0) * P.W + w0) * Fp;
     const int wn = min(32, P.W - w0), hr = min(R, P.H - h0);
     const int per = wn * (Fp >> 2);          // float4s of one strip row on the channels-last side
     const int64_t clrow = (int64_t)P.W * Fp;
@@ -118,19 +120,38 @@ __global__ void add_inplace_scalar_kernel(float* dst, const float* src, int64_t 
 struct SegJobs {
   float* dst[8];
   const float* src[8];
-  int64_t n4[8];      // float4 elements (segments are 16-byte multiples, 16-byte aligned)
+  int64_t n4[8];      // float4 elements of one row (segments are 16-byte multiples, 16-byte aligned)
+  int rows[8];        // rows of the segment (1: a plain contiguous copy) ...
+  int64_t dpitch[8], spitch[8];   // ... and the distance between rows, in floats, on either side
   int nseg, accumulate;
 };
 __global__ void __launch_bounds__(256) seg_copy_kernel(const __grid_constant__ SegJobs J) {
   const int sgm = blockIdx.y;
-  const float4* src = reinterpret_cast<const float4*>(J.src[sgm]);
-  float* dst = J.dst[sgm];
-  const int64_t n4 = J.n4[sgm];
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-    const float4 v = src[i];
-    // accumulate: two neighbours may return gradient for the same frame -> vector RED, not a read-modify-write
-    if (J.accumulate) red_add4(dst + i * 4, v);
-    else reinterpret_cast<float4*>(dst)[i] = v;
+  const int64_t n4 = J.n4[sgm], total = n4 * J.rows[sgm];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const float* sbase = J.src[sgm];
+  float* dbase = J.dst[sgm];
+  // rows x n4 float4s as one index space; four independent 16-byte loads in flight per thread (peer loads over NVLink
+  // have microseconds of latency: parallelism, not per-thread speed, is what fills the link)
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += 4 * stride) {
+    float4 v[4];
+    int64_t off_d[4];
+    bool ok[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int64_t i = i0 + u * stride;
+      ok[u] = i < total;
+      const int64_t r = ok[u] ? i / n4 : 0, c = ok[u] ? i - r * n4 : 0;
+      off_d[u] = r * J.dpitch[sgm] + c * 4;
+      if (ok[u]) v[u] = *reinterpret_cast<const float4*>(sbase + r * J.spitch[sgm] + c * 4);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      if (!ok[u]) continue;
+      // accumulate: two neighbours may return gradient for the same frame -> vector RED, not a read-modify-write
+      if (J.accumulate) red_add4(dbase + off_d[u], v[u]);
+      else *reinterpret_cast<float4*>(dbase + off_d[u]) = v[u];
+    }
   }
 }
 
@@ -193,7 +214,7 @@ extern "C" int stnls_pack_cl(float* dst_cl, const float* src, int B, int HD, int
   LayoutParams P;
   P.cl = dst_cl; P.planar = const_cast<float*>(src); P.HD = HD; P.t0 = t0; P.Tloc = Tloc; P.F = F; P.Fp = Fp;
   P.H = H; P.W = W; P.sB = sB; P.sHD = sHD; P.sT = sT; P.sC = sC; P.counts_h = counts_h; P.counts_w = counts_w;
-  P.accumulate = 0;
+  P.accumulate = 0; P.Tpitch = Tloc; P.tcl0 = 0;
   STNLS_REQUIRE((counts_h == nullptr) == (counts_w == nullptr), "pack_cl: counts_h and counts_w go together");
   return launch_layout(true, P, B, (cudaStream_t)stream, "pack_cl");
 }
@@ -204,7 +225,7 @@ extern "C" int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, i
   LayoutParams P;
   P.cl = const_cast<float*>(src_cl); P.planar = dst; P.HD = HD; P.t0 = t0; P.Tloc = Tloc; P.F = F; P.Fp = Fp;
   P.H = H; P.W = W; P.sB = sB; P.sHD = sHD; P.sT = sT; P.sC = sC; P.counts_h = nullptr; P.counts_w = nullptr;
-  P.accumulate = accumulate;
+  P.accumulate = accumulate; P.Tpitch = Tloc; P.tcl0 = 0;
   return launch_layout(false, P, B, (cudaStream_t)stream, "unpack_cl");
 }
 
@@ -212,7 +233,8 @@ extern "C" int stnls_unpack_cl(float* dst, const float* src_cl, int B, int HD, i
 static int launch_layout_multi(bool pack, int njobs, float* const* cl, float* const* planar, const int* B, const int* HD,
                                const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
                                const int64_t* strides, const int* const* counts_h, const int* const* counts_w,
-                               const int* accumulate, cudaStream_t st, const char* who) {
+                               const int* accumulate, const int* cl_tpitch, const int* cl_t0, cudaStream_t st,
+                               const char* who) {
   STNLS_REQUIRE(njobs >= 1 && njobs <= LAYOUT_MAX_JOBS, "%s: 1..%d videos per launch", who, LAYOUT_MAX_JOBS);
   STNLS_REQUIRE(cl && planar && B && HD && t0 && Tloc && F && H && W && strides, "%s: null argument", who);
   LayoutJobs J;
@@ -223,6 +245,9 @@ static int launch_layout_multi(bool pack, int njobs, float* const* cl, float* co
     P.counts_h = counts_h ? counts_h[j] : nullptr; P.counts_w = counts_w ? counts_w[j] : nullptr;
     STNLS_REQUIRE((P.counts_h == nullptr) == (P.counts_w == nullptr), "%s: counts_h and counts_w go together", who);
     P.accumulate = accumulate ? accumulate[j] : 0;
+    P.Tpitch = cl_tpitch ? cl_tpitch[j] : P.Tloc; P.tcl0 = cl_t0 ? cl_t0[j] : 0;
+    STNLS_REQUIRE(P.tcl0 >= 0 && P.tcl0 + P.Tloc <= P.Tpitch, "%s: frames [%d, %d) outside the %d frames of the channels-last video",
+                  who, P.tcl0, P.tcl0 + P.Tloc, P.Tpitch);
   }
   J.njobs = njobs;
   return launch_layout_jobs(pack, J, B, st, who);
@@ -231,16 +256,17 @@ static int launch_layout_multi(bool pack, int njobs, float* const* cl, float* co
 extern "C" int stnls_pack_cl_multi(int njobs, float* const* dst_cl, const float* const* src, const int* B, const int* HD,
                                    const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
                                    const int64_t* strides, const int* const* counts_h, const int* const* counts_w,
-                                   stnls_stream_t stream) {
+                                   const int* cl_tpitch, const int* cl_t0, stnls_stream_t stream) {
   return launch_layout_multi(true, njobs, dst_cl, const_cast<float* const*>(src), B, HD, t0, Tloc, F, H, W, strides,
-                             counts_h, counts_w, nullptr, (cudaStream_t)stream, "pack_cl_multi");
+                             counts_h, counts_w, nullptr, cl_tpitch, cl_t0, (cudaStream_t)stream, "pack_cl_multi");
 }
 
 extern "C" int stnls_unpack_cl_multi(int njobs, float* const* dst, const float* const* src_cl, const int* B, const int* HD,
                                      const int* t0, const int* Tloc, const int* F, const int* H, const int* W,
-                                     const int64_t* strides, const int* accumulate, stnls_stream_t stream) {
+                                     const int64_t* strides, const int* accumulate, const int* cl_tpitch,
+                                     const int* cl_t0, stnls_stream_t stream) {
   return launch_layout_multi(false, njobs, const_cast<float* const*>(src_cl), dst, B, HD, t0, Tloc, F, H, W, strides,
-                             nullptr, nullptr, accumulate, (cudaStream_t)stream, "unpack_cl_multi");
+                             nullptr, nullptr, accumulate, cl_tpitch, cl_t0, (cudaStream_t)stream, "unpack_cl_multi");
 }
 
 extern "C" int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_stream_t stream) {
@@ -257,8 +283,8 @@ extern "C" int stnls_add_inplace(float* dst, const float* src, int64_t n, stnls_
   return STNLS_OK;
 }
 
-extern "C" int stnls_seg_copy(float* const* dst, const float* const* src, const int64_t* nfloat, int nseg, int accumulate,
-                              stnls_stream_t stream) {
+static int seg_copy_impl(float* const* dst, const float* const* src, const int64_t* nfloat, const int* rows,
+                         const int64_t* dst_pitch, const int64_t* src_pitch, int nseg, int accumulate, stnls_stream_t stream) {
   STNLS_REQUIRE(dst && src && nfloat && nseg >= 0 && nseg <= 8, "seg_copy: 0..8 segments");
   if (nseg == 0) return STNLS_OK;
   SegJobs J;
@@ -268,14 +294,29 @@ extern "C" int stnls_seg_copy(float* const* dst, const float* const* src, const 
     STNLS_REQUIRE(((reinterpret_cast<uintptr_t>(dst[i]) | reinterpret_cast<uintptr_t>(src[i])) & 15) == 0,
                   "seg_copy: segment %d is not 16-byte aligned", i);
     J.dst[i] = dst[i]; J.src[i] = src[i]; J.n4[i] = nfloat[i] / 4;
-    most = J.n4[i] > most ? J.n4[i] : most;
+    J.rows[i] = rows ? rows[i] : 1; J.dpitch[i] = rows ? dst_pitch[i] : 0; J.spitch[i] = rows ? src_pitch[i] : 0;
+    STNLS_REQUIRE(J.rows[i] >= 0 && J.dpitch[i] % 4 == 0 && J.spitch[i] % 4 == 0, "seg_copy: segment %d: bad rows / pitch", i);
+    if (J.rows[i] == 0) J.n4[i] = 0;
+    most = J.n4[i] * J.rows[i] > most ? J.n4[i] * J.rows[i] : most;
   }
   J.nseg = nseg; J.accumulate = accumulate;
   if (most == 0) return STNLS_OK;
-  int64_t bx = (most + 256 * 8 - 1) / (256 * 8);
+  int64_t bx = (most + 256 * 4 - 1) / (256 * 4);
   if (bx > 148 * 16) bx = 148 * 16;
   if (bx < 1) bx = 1;
   seg_copy_kernel<<<dim3((unsigned)bx, (unsigned)nseg), 256, 0, (cudaStream_t)stream>>>(J);
   STNLS_CHECK_LAUNCH("seg_copy");
   return STNLS_OK;
+}
+
+extern "C" int stnls_seg_copy(float* const* dst, const float* const* src, const int64_t* nfloat, int nseg, int accumulate,
+                              stnls_stream_t stream) {
+  return seg_copy_impl(dst, src, nfloat, nullptr, nullptr, nullptr, nseg, accumulate, stream);
+}
+
+extern "C" int stnls_seg_copy2d(float* const* dst, const float* const* src, const int64_t* nfloat, const int* rows,
+                                const int64_t* dst_pitch, const int64_t* src_pitch, int nseg, int accumulate,
+                                stnls_stream_t stream) {
+  STNLS_REQUIRE(rows && dst_pitch && src_pitch, "seg_copy2d: null argument");
+  return seg_copy_impl(dst, src, nfloat, rows, dst_pitch, src_pitch, nseg, accumulate, stream);
 }

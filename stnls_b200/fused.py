@@ -48,11 +48,13 @@ class FusedSearchAggFunction(th.autograd.Function):
     Returns out (B,HD,Tq,Fv,H,W), dists (B,HD,Tq,nH,nW,K), inds (...,K,3)."""
 
     @staticmethod
-    def forward(ctx, q, k, v, flows, search, agg, scale, shard):
+    def forward(ctx, q, k, v, flows, search, agg, scale, shard, halo):
+        """halo: None (k, v hold the owned + halo frames) or a parallel.PeerHaloCL (k, v hold the OWNED frames; the halo
+        frames are exchanged here, in the channels-last layout)."""
         s, a = search, agg
         HD = s.nheads
         B, Tq, C, H, W = q.shape
-        Tk = k.shape[1]
+        Tk = k.shape[1] if halo is None else halo.plan.fb - halo.plan.fa
         F, Fv = C // HD, v.shape[2] // HD
         T, tq0, tk0 = shard_of(shard, Tq)
         W_t = 2 * s.wt + 1
@@ -66,7 +68,19 @@ class FusedSearchAggFunction(th.autograd.Function):
         flows_k = flows.float().contiguous()
         dist_type_i, _ = DIST_MENU[s.dist_type]
         anchor = s.self_action in ("anchor", "anchor_self")
-        q_cl, k_cl, v_cl = ops.pack_cl_multi([q, k, v], HD)
+        if halo is None:
+            q_cl, k_cl, v_cl = ops.pack_cl_multi([q, k, v], HD)
+        else:
+            plan, N = halo.plan, B * HD
+            Fp, Fvp = ops.padded_channels(F), ops.padded_channels(Fv)
+            assert k.shape[1] == v.shape[1] == plan.b - plan.a, "k, v must hold this rank's owned frames"
+            kbuf, khdl = halo.buffer("k", N, H * W * Fp, q.device)
+            vbuf, vhdl = halo.buffer("v", N, H * W * Fvp, q.device)
+            k_cl, v_cl = kbuf.view(N, Tk, H, W, Fp), vbuf.view(N, Tk, H, W, Fvp)
+            own = plan.a - plan.fa
+            q_cl = ops.pack_cl_multi([q, k, v], HD, outs=[None, (k_cl, own), (v_cl, own)])[0]
+            halo.handshake(khdl)
+            halo.pull([(kbuf, khdl), (vbuf, vhdl)])
         geom = ops.make_geom(B, HD, T, F, H, W, H, W, s.stride0, tq0, Tq, tk0, Tk)
         opts = SearchOpts(s.ws, s.wt, 0, 0, s.ps, s.k, s.stride0, s.stride0, s.dilation, float(s.stride1),
                           int(s.reflect_bounds), int(s.full_ws), 0 if s.use_adj else -(s.ps // 2), 0, 0,
@@ -84,7 +98,7 @@ class FusedSearchAggFunction(th.autograd.Function):
         ctx.save_for_backward(q_cl, k_cl, v_cl, inds, flows_k, weights, ch, cw)
         ctx.geom, ctx.opts, ctx.ageom, ctx.aopts = geom, opts, ageom, aopts
         ctx.shapes = (tuple(q.shape), tuple(k.shape), tuple(v.shape))
-        ctx.HD, ctx.scale, ctx.flow_ndim = HD, float(scale), flow_ndim
+        ctx.HD, ctx.scale, ctx.flow_ndim, ctx.halo = HD, float(scale), flow_ndim, halo
         ctx.mark_non_differentiable(dists, inds)
         return out, dists, inds
 
@@ -93,15 +107,30 @@ class FusedSearchAggFunction(th.autograd.Function):
         q_cl, k_cl, v_cl, inds, flows_k, weights, ch, cw = ctx.saved_tensors
         flows_grad = ctx.needs_input_grad[3]
         gout_cl = ops.pack_cl(gout, ctx.HD, counts=(ch, cw))            # fused grad_out / counts
-        gv_cl, gw, gf = ops.wpsum_backward(gout_cl, v_cl, weights, inds, ctx.ageom, ctx.aopts)
+        halo = ctx.halo
+        gk_out = gv_out = None
+        if halo is not None:   # owned + halo gradient videos in symmetric memory: the neighbours read their share there
+            N, Tk, H, W, Fp = k_cl.shape
+            gkbuf, gkhdl = halo.buffer("gk", N, H * W * Fp, k_cl.device)
+            gvbuf, gvhdl = halo.buffer("gv", N, H * W * v_cl.shape[-1], k_cl.device)
+            gkbuf.zero_()
+            gvbuf.zero_()
+            gk_out, gv_out = gkbuf.view(k_cl.shape), gvbuf.view(v_cl.shape)
+        gv_cl, gw, gf = ops.wpsum_backward(gout_cl, v_cl, weights, inds, ctx.ageom, ctx.aopts, gv_out=gv_out)
         gq_cl, gk_cl, gflows = ops.search_backward_sm(q_cl, k_cl, flows_k, gw, weights, ctx.scale, gf, inds, ctx.geom,
-                                                      ctx.opts, flows_grad)
-        gq, gk, gv = ops.unpack_cl_multi([gq_cl, gk_cl, gv_cl], ctx.shapes, ctx.HD)
+                                                      ctx.opts, flows_grad, gk_out=gk_out)
+        if halo is None:
+            gq, gk, gv = ops.unpack_cl_multi([gq_cl, gk_cl, gv_cl], ctx.shapes, ctx.HD)
+        else:
+            halo.handshake(gkhdl)
+            halo.pull_add([(gkbuf, gkhdl), (gvbuf, gvhdl)])
+            own = halo.plan.a - halo.plan.fa
+            gq, gk, gv = ops.unpack_cl_multi([gq_cl, gk_cl, gv_cl], ctx.shapes, ctx.HD, cl_t0=[0, own, own])
         if gflows is not None and ctx.flow_ndim == 6:
             gflows = gflows[:, 0].contiguous()
-        return gq, gk, gv, gflows, None, None, None, None
+        return gq, gk, gv, gflows, None, None, None, None, None
 
 
-def fused_search_agg(search, agg, q, k, v, flows, scale, shard=None):
+def fused_search_agg(search, agg, q, k, v, flows, scale, shard=None, halo=None):
     """scale: signed softmax scale (negative for l2 distances)."""
-    return FusedSearchAggFunction.apply(q, k, v, flows, search, agg, scale, shard)
+    return FusedSearchAggFunction.apply(q, k, v, flows, search, agg, scale, shard, halo)

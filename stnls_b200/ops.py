@@ -104,43 +104,53 @@ def _arr(ctype, vals):
 
 def pack_cl_multi(vids, nheads, outs=None):
     """[planar video] -> [channels-last copy] in ONE launch (at most 4 videos, same head count; q, k, v of a step).
-    outs: optional preallocated destinations (e.g. views into a symmetric-memory buffer)."""
+    outs[i]: None, or (buffer (N, Tpitch, H, W, Fp), first frame): the video's frames are written into the buffer starting
+    at that frame (a rank packs its own frames straight into the owned + halo buffer its peers read)."""
     _need_cuda(*vids)
     assert 1 <= len(vids) <= 4
     info = [_planar_strides(v, nheads) for v in vids]
-    res, B_, HD_, t0_, Tl_, F_, H_, W_, st_ = [], [], [], [], [], [], [], [], []
+    res, B_, HD_, t0_, Tl_, F_, H_, W_, st_, tp_, tc_ = [], [], [], [], [], [], [], [], [], [], []
     for i, (vid, (B, HD, T, F, H, W), strides) in enumerate(info):
-        shape = (B * HD, T, H, W, padded_channels(F))
-        out = th.empty(shape, device=vid.device, dtype=th.float32) if outs is None else outs[i]
-        assert tuple(out.shape) == shape and out.is_contiguous() and out.dtype == th.float32
+        dst = None if outs is None else outs[i]
+        if dst is None:
+            out, tc = th.empty((B * HD, T, H, W, padded_channels(F)), device=vid.device, dtype=th.float32), 0
+        else:
+            out, tc = dst
+            assert out.is_contiguous() and out.dtype == th.float32 and out.shape[0] == B * HD and out.shape[1] >= tc + T
+            assert tuple(out.shape[2:]) == (H, W, padded_channels(F))
         res.append(out)
         B_.append(B); HD_.append(HD); t0_.append(0); Tl_.append(T); F_.append(F); H_.append(H); W_.append(W)
-        st_ += list(strides)
+        st_ += list(strides); tp_.append(out.shape[1]); tc_.append(tc)
     n = len(vids)
     _launch("pack_cl", _C.lib().stnls_pack_cl_multi, n, _arr(ctypes.c_void_p, [o.data_ptr() for o in res]),
             _arr(ctypes.c_void_p, [v.data_ptr() for v, _, _ in info]), _arr(ctypes.c_int, B_), _arr(ctypes.c_int, HD_),
             _arr(ctypes.c_int, t0_), _arr(ctypes.c_int, Tl_), _arr(ctypes.c_int, F_), _arr(ctypes.c_int, H_),
-            _arr(ctypes.c_int, W_), _arr(ctypes.c_int64, st_), None, None, _stream())
+            _arr(ctypes.c_int, W_), _arr(ctypes.c_int64, st_), None, None, _arr(ctypes.c_int, tp_),
+            _arr(ctypes.c_int, tc_), _stream())
     return res
 
 
-def unpack_cl_multi(cls, shapes, nheads):
-    """[channels-last] -> [planar tensor of shape] in ONE launch (at most 4; the three gradients of a step)."""
+def unpack_cl_multi(cls, shapes, nheads, cl_t0=None):
+    """[channels-last] -> [planar tensor of shape] in ONE launch (at most 4; the three gradients of a step).
+    cl_t0[i]: first frame of cls[i] to unpack (the owned slice of an owned + halo gradient); default 0."""
     _need_cuda(*cls)
     assert 1 <= len(cls) <= 4 and len(cls) == len(shapes)
-    outs, B_, HD_, t0_, Tl_, F_, H_, W_, st_ = [], [], [], [], [], [], [], [], []
-    for cl, shape in zip(cls, shapes):
+    outs, B_, HD_, t0_, Tl_, F_, H_, W_, st_, tp_, tc_ = [], [], [], [], [], [], [], [], [], [], []
+    for i, (cl, shape) in enumerate(zip(cls, shapes)):
         out = th.empty(shape, device=cl.device, dtype=th.float32)
         _, (B, HD, T, F, H, W), strides = _planar_strides(out, nheads)
-        assert tuple(cl.shape) == (B * HD, T, H, W, padded_channels(F)) and cl.is_contiguous()
+        tc = 0 if cl_t0 is None else cl_t0[i]
+        assert cl.is_contiguous() and cl.shape[0] == B * HD and cl.shape[1] >= tc + T
+        assert tuple(cl.shape[2:]) == (H, W, padded_channels(F))
         outs.append(out)
         B_.append(B); HD_.append(HD); t0_.append(0); Tl_.append(T); F_.append(F); H_.append(H); W_.append(W)
-        st_ += list(strides)
+        st_ += list(strides); tp_.append(cl.shape[1]); tc_.append(tc)
     n = len(cls)
     _launch("unpack_cl", _C.lib().stnls_unpack_cl_multi, n, _arr(ctypes.c_void_p, [o.data_ptr() for o in outs]),
             _arr(ctypes.c_void_p, [c.data_ptr() for c in cls]), _arr(ctypes.c_int, B_), _arr(ctypes.c_int, HD_),
             _arr(ctypes.c_int, t0_), _arr(ctypes.c_int, Tl_), _arr(ctypes.c_int, F_), _arr(ctypes.c_int, H_),
-            _arr(ctypes.c_int, W_), _arr(ctypes.c_int64, st_), None, _stream())
+            _arr(ctypes.c_int, W_), _arr(ctypes.c_int64, st_), None, _arr(ctypes.c_int, tp_), _arr(ctypes.c_int, tc_),
+            _stream())
     return outs
 
 
@@ -313,6 +323,19 @@ def seg_copy(pairs, accumulate=False):
         src = (ctypes.c_void_p * n)(*[s_.data_ptr() for _, s_ in chunk])
         cnt = (ctypes.c_int64 * n)(*[d.numel() for d, _ in chunk])
         _launch("seg_copy", _C.lib().stnls_seg_copy, dst, src, cnt, n, int(accumulate), _stream())
+
+
+def seg_copy2d(jobs, accumulate=False):
+    """jobs: [(dst_ptr, src_ptr, nfloat, rows, dst_pitch, src_pitch)] raw device addresses (src may be peer memory):
+    rows runs of nfloat floats each, copied -- or added with vector REDs -- in ONE launch per 8 jobs."""
+    jobs = [j for j in jobs if j[2] > 0 and j[3] > 0]
+    for i in range(0, len(jobs), 8):
+        ch = jobs[i:i + 8]
+        n = len(ch)
+        _launch("seg_copy", _C.lib().stnls_seg_copy2d, _arr(ctypes.c_void_p, [j[0] for j in ch]),
+                _arr(ctypes.c_void_p, [j[1] for j in ch]), _arr(ctypes.c_int64, [j[2] for j in ch]),
+                _arr(ctypes.c_int, [j[3] for j in ch]), _arr(ctypes.c_int64, [j[4] for j in ch]),
+                _arr(ctypes.c_int64, [j[5] for j in ch]), n, int(accumulate), _stream())
 
 
 def seg_copy_ok(*ts):

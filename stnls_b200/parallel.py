@@ -10,6 +10,8 @@ send halo frames (NCCL send/recv over NVLink, grouped in one batch).  Backward: 
 reversed, carrying grad_k / grad_v halo slices that are SUMMED into the owner.  No all-reduce, no
 all-gather of full tensors.
 """
+import os
+
 import torch as th
 import torch.distributed as dist
 
@@ -314,6 +316,81 @@ class PeerHalo:
         return gowns
 
 
+class PeerHaloCL:
+    """Halo exchange in the kernels' own CHANNELS-LAST layout, used by the one-node step (stnls_b200/fused.py).
+
+    A rank's owned + halo key / value videos (N, n_ext, H, W, Fp) live in symmetric memory.  The pack kernel writes the
+    owned frames straight into them, a neighbour-only handshake on the allocation's signal pads (put_signal /
+    wait_signal towards the ranks this rank exchanges frames with -- no group-wide barrier) makes them visible, and ONE
+    segmented-copy launch pulls the halo frames of every tensor from every neighbour over NVLink.  Backward: the
+    kernels accumulate into owned + halo gradient videos in symmetric memory, after the handshake ONE launch adds the
+    slices lent to the neighbours (vector REDs) into the owned slice, which the unpack kernel reads in place.
+    Per step: 2 copy launches and 2 handshakes (the planar exchange of PeerHalo: 5 copy launches, 2 group barriers).
+    Buffers are double-buffered: a rank rewrites a buffer two exchanges after its neighbours read it, and has waited
+    for their next signal in between."""
+
+    def __init__(self, plan, group=None, timeout_ms=30000):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.symm_mem, self.plan, self.timeout_ms = symm_mem, plan, timeout_ms
+        self.group = dist.group.WORLD if group is None else group
+        self.nbrs = sorted({r for r, _, _ in plan.recvs()} | {r for r, _, _ in plan.sends()})
+        self.max_ext = max(fb - fa for fa, fb in plan.need)
+        self.bufs, self.count = {}, {}
+
+    def buffer(self, tag, N, frame, device):
+        """(view (N, n_ext, frame) of this rank's buffer, handle); every rank allocates N * max_ext * frame floats."""
+        key = (tag, N, frame)
+        if key not in self.bufs:
+            pair = []
+            for _ in range(2):
+                t = self.symm_mem.empty((N * self.max_ext * frame,), dtype=th.float32, device=device)
+                pair.append((t, self.symm_mem.rendezvous(t, self.group)))
+            self.bufs[key] = pair
+            self.count[key] = 0
+        i = self.count[key]
+        self.count[key] = i + 1
+        t, hdl = self.bufs[key][i % 2]
+        n_ext = self.plan.fb - self.plan.fa
+        return t[:N * n_ext * frame].view(N, n_ext, frame), hdl
+
+    def handshake(self, hdl):
+        for r in self.nbrs:
+            hdl.put_signal(r, 0, self.timeout_ms)
+        for r in self.nbrs:
+            hdl.wait_signal(r, 0, self.timeout_ms)
+
+    def _peer_ptr(self, hdl, rank, N, frame):
+        return hdl.get_buffer(rank, (N * self.max_ext * frame,), th.float32).data_ptr()
+
+    def pull(self, items):
+        """items: [(view, hdl)] packed owned frames in place; fetch the halo frames of each from the neighbours."""
+        from . import ops
+        plan = self.plan
+        jobs = []
+        for view, hdl in items:
+            N, n_ext, frame = view.shape
+            for src, lo, hi in plan.recvs():
+                fa_s, fb_s = plan.need[src]
+                jobs.append((view.data_ptr() + (lo - plan.fa) * frame * 4,
+                             self._peer_ptr(hdl, src, N, frame) + (lo - fa_s) * frame * 4,
+                             (hi - lo) * frame, N, n_ext * frame, (fb_s - fa_s) * frame))
+        ops.seg_copy2d(jobs)
+
+    def pull_add(self, items):
+        """items: [(view, hdl)] owned + halo gradients; add what the neighbours accumulated for this rank's frames."""
+        from . import ops
+        plan = self.plan
+        jobs = []
+        for view, hdl in items:
+            N, n_ext, frame = view.shape
+            for dst, lo, hi in plan.sends():
+                fa_d, fb_d = plan.need[dst]
+                jobs.append((view.data_ptr() + (lo - plan.fa) * frame * 4,
+                             self._peer_ptr(hdl, dst, N, frame) + (lo - fa_d) * frame * 4,
+                             (hi - lo) * frame, N, n_ext * frame, (fb_d - fa_d) * frame))
+        ops.seg_copy2d(jobs, accumulate=True)
+
+
 class PeerHaloExchangeMulti(th.autograd.Function):
     """k and v (any number of planar videos) through ONE peer-memory exchange per direction (PeerHalo.forward_multi)."""
 
@@ -360,6 +437,7 @@ class ShardedSearchAgg(th.nn.Module):
         super().__init__()
         self.search, self.agg, self.plan, self.scale, self.group = search, agg, plan, scale, group
         self.peer = None
+        self.peer_cl = None
         self.halo_kind = "none" if plan.world == 1 else "nccl"
         if plan.world > 1 and halo in ("peer", "auto") and th.cuda.is_available() and dist.get_backend() == "nccl":
             err = None
@@ -380,6 +458,16 @@ class ShardedSearchAgg(th.nn.Module):
     def forward(self, q, k, v, flows, v_ready=None):
         """v_ready: optional CUDA event after which `v` is valid (e.g. its host->device copy on a side stream);
         the current stream waits for it only when the aggregation needs v, so the copy overlaps the search."""
+        if self.peer is not None and v_ready is None and os.environ.get("STNLS_HALO_CL", "1") != "0":
+            from . import fused
+            if fused.fusable(self.search, self.agg, q, k, v, flows):
+                # one node for exchange + step: k / v packed straight into symmetric memory, halo frames pulled in the
+                # channels-last layout, neighbour-only handshakes (PeerHaloCL)
+                if self.peer_cl is None:
+                    self.peer_cl = PeerHaloCL(self.plan, self.group)
+                sign = -1.0 if self.search.dist_type == "l2" else 1.0
+                return fused.fused_search_agg(self.search, self.agg, q, k, v, flows, sign * self.scale,
+                                              shard=self.plan.shard, halo=self.peer_cl)
         joint = self.peer is not None and v_ready is None and PeerHalo.fast_ok([k, v])
         if joint:   # k and v in one exchange: one barrier and two copy launches for both (and for both gradients)
             k_ext, v_ext = PeerHaloExchangeMulti.apply(self.peer, "kv", k, v)

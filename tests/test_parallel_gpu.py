@@ -37,6 +37,10 @@ def _worker(rank, world, halo, port, ret):
         (out * gout[:, :, sl].to(dev)).sum().backward()
         return [out.detach(), dists.detach(), inds.detach()] + [x.grad for x in ins] + [fl.grad], model.halo_kind
 
+    # "peer": planar exchange (PeerHalo) around the module chain / one-node step; "peer_cl": exchange in the channels-last
+    # layout inside the one-node step (PeerHaloCL, neighbour-only handshakes) -- the default when peer memory works
+    os.environ["STNLS_HALO_CL"] = "1" if halo == "peer_cl" else "0"
+    halo = "peer" if halo == "peer_cl" else halo
     plan = parallel.ShardPlan(T, wt, world, rank)
     got, kind = run(plan, halo, slice(plan.a, plan.b))
     assert kind == halo, f"halo path {kind} != requested {halo}"
@@ -67,7 +71,7 @@ def _worker(rank, world, halo, port, ret):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("halo", ["nccl", "peer"])
+@pytest.mark.parametrize("halo", ["nccl", "peer", "peer_cl"])
 def test_sharded_matches_single(halo):
     if th.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")
@@ -75,7 +79,7 @@ def test_sharded_matches_single(halo):
     world = 2
     mgr = mp.Manager()
     ret = mgr.dict()
-    port = 29600 + (os.getpid() % 300) + (1 if halo == "peer" else 0)
+    port = 29600 + (os.getpid() % 300) + {"nccl": 0, "peer": 1, "peer_cl": 2}[halo]
     mp.spawn(_worker, args=(world, halo, port, ret), nprocs=world, join=True)
     assert len(ret) == world
     for rank, errs in ret.items():
