@@ -561,7 +561,7 @@ def run_product(args):
     t_ms, e2e_ms, lat_ms, e2e_eager_ms = float(tt[0]), float(tt[1]), float(tt[3]), float(tt[4])
     if graph_ms is not None:
         graph_ms = float(tt[2])
-    return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
+    return dict(world=world, rank=rank, wl=wl, plan=plan, halo=model.halo_kind, halo_path=getattr(model, "halo_path", None), t_ms=t_ms, e2e_ms=e2e_ms, timeline=timeline,
                 launches=launches, clocks=clk.summary(), h2d=h2d, d2h=d2h, graph_ms=graph_ms, graph_note=graph_note,
                 per_graph=per_graph, unit=unit, lat_ms=lat_ms, e2e_from=e2e_from, e2e_eager_ms=e2e_eager_ms, numa=numa,
                 h2d_gbs=h2d_gbs, d2h_gbs=d2h_gbs)
@@ -1010,7 +1010,7 @@ def main():
     line = {"metric": "search+agg fwd+bwd throughput", "value": value, "unit": "Gcandidates/s",
             "n_gpus": world, "steps": steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": dict(describe(wl, args.workload, world), halo=r["halo"]),
+            "data": "synthetic", "config": dict(describe(wl, args.workload, world), halo=r["halo"], **({"halo_path": r["halo_path"]} if r.get("halo_path") else {})),
             "frames_per_s": wl["B"] * wl["T"] * world / (ms_per_step * 1e-3),
             "e2e": {"value": e2e_val, "unit": "Gcandidates/s", "h2d_bytes_per_step": r["h2d"],
                     "d2h_bytes_per_step": r["d2h"], "ms_per_step": e2e_ms,

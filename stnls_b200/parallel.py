@@ -438,6 +438,7 @@ class ShardedSearchAgg(th.nn.Module):
         self.search, self.agg, self.plan, self.scale, self.group = search, agg, plan, scale, group
         self.peer = None
         self.peer_cl = None
+        self.halo_path = None    # set on first use: which exchange the forward pass actually took
         self.halo_kind = "none" if plan.world == 1 else "nccl"
         if plan.world > 1 and halo in ("peer", "auto") and th.cuda.is_available() and dist.get_backend() == "nccl":
             err = None
@@ -465,6 +466,7 @@ class ShardedSearchAgg(th.nn.Module):
                 # channels-last layout, neighbour-only handshakes (PeerHaloCL)
                 if self.peer_cl is None:
                     self.peer_cl = PeerHaloCL(self.plan, self.group)
+                    self.halo_path = "peer memory, channels-last frames pulled inside the one-node step, neighbour handshakes"
                 sign = -1.0 if self.search.dist_type == "l2" else 1.0
                 return fused.fused_search_agg(self.search, self.agg, q, k, v, flows, sign * self.scale,
                                               shard=self.plan.shard, halo=self.peer_cl)
