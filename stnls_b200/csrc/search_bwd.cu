@@ -37,7 +37,7 @@ struct BwdParams {
   const uint8_t* reflect;
   stnls_geom g;
   stnls_search_opts o;
-  int K, mode, nquad, W_t, fast3, ksplit, qagg;
+  int K, mode, nquad, W_t, fast3, ksplit, qagg, rolled;
   int idx32;                                  // launch shape of frame_grid(): thread index decoded with the FastDivs
   unsigned per_frame, frames;
   unsigned gx, gy, gz;
@@ -313,6 +313,49 @@ __global__ void __launch_bounds__(128, (FAST && !KSPLIT) ? 3 : SB_MINB) search_b
         float4 A[4], B[4], accA[4], accB[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) { A[j] = ldg4(vr + j * g.Fp); accA[j] = f4zero(); }
+        if (KSPLIT && P.rolled) {
+          // one neighbour per thread: the three patch rows as a ROLLED loop -- a third of the straight-line code, for
+          // a launch whose warps each run the path once (instruction fetch, not reuse, feeds them)
+#pragma unroll 1
+          for (int pi = 0; pi < 3; pi++) {
+            const float n1 = z.pph + (float)(pi + po);
+            const int a0 = __float2int_rz(n1);
+            const float g0 = fmaxf(0.f, 1 - fabsf(a0 - n1)), g1 = fmaxf(0.f, 1 - fabsf((a0 + 1) - n1));
+#pragma unroll
+            for (int j = 0; j < 4; j++) { B[j] = ldg4(vr + (pi + 1) * rs + j * g.Fp); accB[j] = f4zero(); }
+#pragma unroll
+            for (int pj = 0; pj < 3; pj++) {
+              const int64_t qo = ((int64_t)(rh + pi + po) * g.qW + (rw + pj + po)) * g.Fp;
+              const float4 x0 = ldg4(qf + qo);
+              const float w00 = g0 * gw[pj][0], w01 = g0 * gw[pj][1];
+              const float w10 = g1 * gw[pj][0], w11 = g1 * gw[pj][1];
+              float4 x1 = f4zero();
+              fma4(x1, w00, A[pj]); fma4(x1, w01, A[pj + 1]); fma4(x1, w10, B[pj]); fma4(x1, w11, B[pj + 1]);
+              float4 a0_, a1;
+              if (DIST == 0) { a0_ = f4scale(x1, weight); a1 = f4scale(x0, weight); }
+              else {
+                const float w2 = weight * 2;
+                a0_ = make_float4(w2 * (x0.x - x1.x), w2 * (x0.y - x1.y), w2 * (x0.z - x1.z), w2 * (x0.w - x1.w));
+                a1 = make_float4(-a0_.x, -a0_.y, -a0_.z, -a0_.w);
+              }
+              red_add4(gqf + qo, a0_);
+              fma4(accA[pj], w00, a1); fma4(accA[pj + 1], w01, a1);
+              fma4(accB[pj], w10, a1); fma4(accB[pj + 1], w11, a1);
+              if (MODE >= 2) {
+                const float d00 = dot4(A[pj], a1), d01 = dot4(A[pj + 1], a1);
+                const float d10 = dot4(B[pj], a1), d11 = dot4(B[pj + 1], a1);
+                dfw += g0 * (d01 - d00) + g1 * (d11 - d10);
+                dfh += gw[pj][0] * (d10 - d00) + gw[pj][1] * (d11 - d01);
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) { red_add4(gr_ + pi * rs + j * g.Fp, accA[j]); A[j] = B[j]; accA[j] = accB[j]; }
+          }
+#pragma unroll
+          for (int j = 0; j < 4; j++) red_add4(gr_ + 3 * rs + j * g.Fp, accA[j]);
+          tail(z, dfw, dfh);
+          continue;
+        }
 #pragma unroll
         for (int pi = 0; pi < 3; pi++) {
 #pragma unroll
@@ -429,6 +472,7 @@ static int search_backward_impl(float* gq_cl, float* gk_cl, float* grad_flows, c
   P.ksplit = (P.mode != 0 && o->ps >= 2 && P.nthreads < (1 << 20)) ? 1 : 0;
   if (env_ks) P.ksplit = (env_ks[0] == '1' && P.mode != 0) ? 1 : 0;
   if (P.ksplit) P.nthreads *= K;
+  { const char* e = getenv("STNLS_SB_ROLLED"); P.rolled = (e && e[0] == '0') ? 0 : 1; }   // C2: 0.551 -> 0.513 ms
   STNLS_REQUIRE(P.nthreads / 128 < 2147483647LL, "search_backward: too many threads for one launch");
   {
     const int64_t per_frame = (int64_t)g->nH * g->nW * P.nquad * (P.ksplit ? K : 1), frames = (int64_t)g->B * g->HD * g->Tq;
