@@ -49,6 +49,7 @@ struct TileCfg {
   int cand_pitch;          // floats between two candidates in the scratch (Fp + 4: conflict-free LDS.128)
   int q_stride;            // floats between the scratch areas of two queries of a warp
   int smem_bytes;
+  int rolled;              // steady-state rows of the core as a rolled loop (tile_core_rolled), where the window allows
 };
 
 // host side (search_fwd_tile_host.cu): builds the tensor map + configuration and launches; returns
@@ -174,6 +175,93 @@ __device__ __forceinline__ void tile_core(const float* __restrict__ bp, const in
     }
 #pragma unroll
     for (int y = 0; y <= MC; y++) prev[y] = cur[y];
+  }
+}
+
+// The same core with the steady-state lattice rows as a ROLLED loop over groups of PS rows (needs WH % PS == 0): inside
+// a group the accumulator of a candidate row (i % PS) and the fill of the pending batch are compile-time again -- a group
+// starts with an empty batch and ends by flushing what is left -- so nothing is indexed dynamically, and the code is
+// (PS - 1) + PS lattice rows and two or three flush sites instead of WH + PS - 1 rows and WH * WW / FL sites.  At
+// ws = 9, ps = 3 the unrolled core is ~5 k instructions that every warp streams through once per (query, frame): ncu
+// shows `no_instruction` as its second stall reason (profiles/r02_z_ncu_final.json).
+template <int WH, int WW, int PS, int DIST, int FP, int FL, class Flush>
+__device__ __forceinline__ void tile_core_rolled(const float* __restrict__ bp, const int rowpitch, const float fh,
+                                                 const float fw, const float (&qv)[PS * PS], Flush&& flush) {
+  static_assert(PS > 1 && WH % PS == 0 && WH >= 2 * PS, "tile_core_rolled: whole groups of PS candidate rows");
+  constexpr int MC = WW + PS - 1, G = WH / PS;
+  constexpr int PMAX = FL + WW;
+  const float gh0 = 1.f - fh, gw0 = 1.f - fw;
+  float prev[MC + 1], cur[MC + 1];
+#pragma unroll
+  for (int y = 0; y <= MC; y++) prev[y] = bp[y * FP];
+  float acc[PS][WW];
+#pragma unroll
+  for (int s = 0; s < PS; s++)
+#pragma unroll
+    for (int j = 0; j < WW; j++) acc[s][j] = 0.f;
+  float L[MC];
+  auto lattice_row = [&](const float* rp) {   // raw row -> interpolated lattice row L, raw row becomes `prev`
+#pragma unroll
+    for (int y = 0; y <= MC; y++) cur[y] = rp[y * FP];
+    float v0 = fmaf(fh, cur[0], gh0 * prev[0]);
+#pragma unroll
+    for (int y = 0; y < MC; y++) {
+      const float v1 = fmaf(fh, cur[y + 1], gh0 * prev[y + 1]);
+      L[y] = fmaf(fw, v1, gw0 * v0);
+      v0 = v1;
+    }
+#pragma unroll
+    for (int y = 0; y <= MC; y++) prev[y] = cur[y];
+  };
+  // head: lattice rows 0 .. PS-2 feed candidate rows 0 .. PS-2, none is complete yet
+#pragma unroll
+  for (int x = 0; x < PS - 1; x++) {
+    lattice_row(bp + (x + 1) * rowpitch);
+#pragma unroll
+    for (int pi = 0; pi <= x; pi++)
+#pragma unroll
+      for (int j = 0; j < WW; j++)
+#pragma unroll
+        for (int pj = 0; pj < PS; pj++) acc[x - pi][j] = acc1<DIST>(acc[x - pi][j], qv[pi * PS + pj], L[j + pj]);
+  }
+#pragma unroll 1
+  for (int g = 0; g < G; g++) {
+    float pend[PMAX];
+    int np = 0;                       // compile-time inside the group
+    int lin0 = g * PS * WW;
+    const float* rp = bp + (PS + PS * g) * rowpitch;   // raw row x + 1 of lattice row x = PS - 1 + PS * g
+#pragma unroll
+    for (int r = 0; r < PS; r++) {
+      lattice_row(rp + r * rowpitch);
+#pragma unroll
+      for (int pi = 0; pi < PS; pi++) {
+        const int s = r + PS - 1 - pi;          // candidate row PS * g + s
+        if (s < PS || g + 1 < G) {               // s >= PS: a row of the NEXT group -- there is none after the last
+#pragma unroll
+          for (int j = 0; j < WW; j++)
+#pragma unroll
+            for (int pj = 0; pj < PS; pj++) acc[s % PS][j] = acc1<DIST>(acc[s % PS][j], qv[pi * PS + pj], L[j + pj]);
+        }
+      }
+      // candidate row PS * g + r is complete
+#pragma unroll
+      for (int j = 0; j < WW; j++) {
+        pend[np + j] = acc[r][j];
+        acc[r][j] = 0.f;
+      }
+      np += WW;
+#pragma unroll
+      for (int rep = 0; rep < (PMAX + FL - 1) / FL; rep++) {
+        if (np >= FL || (r == PS - 1 && np > 0)) {
+          const int nv = np < FL ? np : FL;
+          flush(lin0, nv, pend);
+#pragma unroll
+          for (int j = 0; j < PMAX - FL; j++) pend[j] = pend[j + FL];
+          lin0 += nv;
+          np -= nv;
+        }
+      }
+    }
   }
 }
 
@@ -604,7 +692,13 @@ search_fwd_tile_kernel(const __grid_constant__ FwdParams P, const __grid_constan
           }
           __syncwarp();
         };
-        tile_core<WH, WW, PS, DIST, FP, FL>(bp, rowpitch, ph - flh, pw - flw, qv, flush);
+        constexpr bool ROLLABLE = !HALF && PS > 1 && WH % PS == 0 && WH >= 2 * PS;
+        if constexpr (ROLLABLE) {
+          if (C.rolled) tile_core_rolled<WH, WW, PS, DIST, FP, FL>(bp, rowpitch, ph - flh, pw - flw, qv, flush);
+          else tile_core<WH, WW, PS, DIST, FP, FL>(bp, rowpitch, ph - flh, pw - flw, qv, flush);
+        } else {
+          tile_core<WH, WW, PS, DIST, FP, FL>(bp, rowpitch, ph - flh, pw - flw, qv, flush);
+        }
       };
       if (!HALF) {
         run_window(std::integral_constant<int, WS>(), std::integral_constant<int, WS>(), 0, 0);
