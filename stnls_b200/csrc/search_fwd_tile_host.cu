@@ -113,7 +113,6 @@ int launch_tile(const FwdParams& P, cudaStream_t st) {
       if (carve(P, C, nb) + 1024 <= limit) planned = true;
     }
   if (!planned) return 0;
-  C.rolled = getenv("STNLS_FWD_ROLLED") ? 1 : 0;
 
   // ---- tensor map: k_cl as (Fp, kW, kH, N*Tk), box (Fp, BW, BH, 1), zero fill outside ----
   CUtensorMap map;
