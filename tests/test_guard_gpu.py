@@ -78,3 +78,39 @@ def test_no_write_outside_the_declared_buffers(itype, stride1, F, H, W, cuda):
     out.check("wpsum_forward out"); gv.check("wpsum_backward grad_v"); gw.check("wpsum_backward grad_weights")
     gf.check("wpsum_backward grad_flows")
     assert bool(th.isfinite(out.win).all()) and bool(th.isfinite(gv.win).all())
+
+
+@pytest.mark.parametrize("itype,tile", [("float", "1"), ("float", "0"), ("int", "1")])
+def test_nan_pixels_leave_no_output_slot_unwritten(itype, tile, cuda, monkeypatch):
+    """NaN / inf pixels in q and k (a diverging training run): the reference returns a full arg-sorted list, so every slot
+    of dists / inds must be WRITTEN -- the wrappers allocate them uninitialised and the backward dereferences inds.
+    Through the C ABI into sentinel-filled buffers, tile kernel and table kernel (STNLS_FWD_TILE=0), float and int."""
+    monkeypatch.setenv("STNLS_FWD_TILE", tile)
+    L = _C.lib()
+    B, HD, T, F, H, W, ws, wt, ps, K = 1, 2, 3, 16, 40, 36, 5, 1, 3, 9
+    g = th.Generator().manual_seed(21)
+    q, k = [th.randn(B, T, F, H, W, generator=g) for _ in range(2)]
+    k[0, 1, 3, 10:14, 8:30] = float("nan")
+    k[0, 2, :, 20, 20] = float("inf")
+    q[0, 0, 5, 30:33, 5:9] = float("nan")
+    k[0, 0] = float("nan")                       # a whole key frame
+    isint = itype == "int"
+    shape = (B, 1, T, 2 * wt, 2, H, W)
+    fl = th.rand(shape, generator=g) * 3 - 1.5
+    fl = (fl.round().int() if isint else fl).to(cuda).contiguous()
+    q_cl, k_cl = ops.pack_cl(q.to(cuda), HD), ops.pack_cl(k.to(cuda), HD)
+    geom = ops.make_geom(B, HD, T, F // HD, H, W, H, W, 1)
+    opts = _C.SearchOpts(ws, wt, 0, 0, ps, K, 1, 1, 1, 1.0, 1, 1, -(ps // 2), 0, 0, 1, int(isint), 1, 1, 1)
+    nq = B * HD * T * H * W
+    dists = th.full((nq * K,), SENT, device=cuda)
+    inds = th.full((nq * K * 3,), -777, dtype=th.int32, device=cuda) if isint else th.full((nq * K * 3,), SENT, device=cuda)
+    st = ctypes.c_void_p(th.cuda.current_stream().cuda_stream)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    _C.check(L.stnls_search_forward(p(q_cl), p(k_cl), p(fl), p(dists), p(inds), None, None, ctypes.byref(geom),
+                                    ctypes.byref(opts), st))
+    th.cuda.synchronize()
+    assert int((dists == SENT).sum()) == 0, "dists slots left unwritten"
+    assert int((inds == (-777 if isint else SENT)).sum()) == 0, "inds slots left unwritten"
+    iv = inds.view(nq, K, 3).float()
+    # the temporal window shifts at the ends of the clip (up to 2*wt frames to one side)
+    assert bool((iv[..., 0].abs() <= 2 * wt).all()) and bool((iv[..., 1:].abs() < 64).all()), "indices outside any window"
