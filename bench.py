@@ -990,7 +990,7 @@ def main():
     else:
         roofline.update({"bound": "hbm", "achieved": hbm_ach, "peak": peak, "unit": "GB/s", "frac": hbm_ach / peak,
                          "peak_source": peak_src,
-                         "note": "scatter kernel: its limiter is the L2 atomic (RED) rate, DRAM traffic == algorithmic"})
+                         "note": "scatter kernel: limited by gather latency / the L1 pipe at ~21 % occupancy (vector REDs measured at 13-19 % of it, DESIGN.md 3.2); DRAM traffic == algorithmic"})
     fwd = kt.get("search_forward")
     roofline_fma = None
     if fwd:
