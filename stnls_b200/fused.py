@@ -116,9 +116,27 @@ class FusedSearchAggFunction(th.autograd.Function):
             gkbuf.zero_()
             gvbuf.zero_()
             gk_out, gv_out = gkbuf.view(k_cl.shape), gvbuf.view(v_cl.shape)
-        gv_cl, gw, gf = ops.wpsum_backward(gout_cl, v_cl, weights, inds, ctx.ageom, ctx.aopts, gv_out=gv_out)
+        # every other accumulator out of ONE zero-filled workspace (one fill launch instead of six)
+        shapes = [q_cl.shape, weights.shape, inds.shape]
+        if flows_grad:
+            shapes.append(flows_k.shape)
+        if halo is None:
+            shapes += [k_cl.shape, v_cl.shape]
+        offs, total = [], 0
+        for shp in shapes:
+            offs.append(total)
+            total += (shp.numel() + 3) // 4 * 4          # 16-byte aligned pieces
+        ws = th.zeros(total, device=q_cl.device, dtype=th.float32)
+        parts = [ws[o:o + shp.numel()].view(shp) for o, shp in zip(offs, shapes)]
+        gq_out, gw_out, gf_out = parts[:3]
+        gflows_out = parts[3] if flows_grad else None
+        if halo is None:
+            gk_out, gv_out = parts[-2], parts[-1]
+        gv_cl, gw, gf = ops.wpsum_backward(gout_cl, v_cl, weights, inds, ctx.ageom, ctx.aopts, gv_out=gv_out, gw_out=gw_out,
+                                           gf_out=gf_out)
         gq_cl, gk_cl, gflows = ops.search_backward_sm(q_cl, k_cl, flows_k, gw, weights, ctx.scale, gf, inds, ctx.geom,
-                                                      ctx.opts, flows_grad, gk_out=gk_out)
+                                                      ctx.opts, flows_grad, gk_out=gk_out, gq_out=gq_out,
+                                                      gflows_out=gflows_out)
         if halo is None:
             gq, gk, gv = ops.unpack_cl_multi([gq_cl, gk_cl, gv_cl], ctx.shapes, ctx.HD)
         else:

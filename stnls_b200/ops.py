@@ -208,17 +208,17 @@ def search_backward(q_cl, k_cl, flows, grad_dists, grad_inds, inds, kselect, ref
 
 
 def search_backward_sm(q_cl, k_cl, flows, grad_weights, weights, scale, grad_inds, inds, geom, opts, flows_grad,
-                       gk_out=None):
+                       gk_out=None, gq_out=None, gflows_out=None):
     """search_backward with the normalise step's backward folded in (grad_dists computed from grad_weights, weights).
-    gk_out: optional pre-zeroed accumulator for grad_k (e.g. a symmetric-memory buffer)."""
+    *_out: optional PRE-ZEROED accumulators (views of one workspace, a symmetric-memory buffer, ...)."""
     _need_cuda(q_cl, k_cl, grad_weights, weights, inds)
     K = weights.shape[-1]
     assert grad_weights.is_contiguous() and weights.is_contiguous() and inds.is_contiguous()
-    gq = th.zeros_like(q_cl)
+    gq = th.zeros_like(q_cl) if gq_out is None else gq_out
     gk = th.zeros_like(k_cl) if gk_out is None else gk_out
     gflows = None
     if flows_grad:
-        gflows = th.zeros_like(flows, dtype=th.float32)
+        gflows = th.zeros_like(flows, dtype=th.float32) if gflows_out is None else gflows_out
         assert grad_inds is not None and grad_inds.is_contiguous() and grad_inds.dtype == th.float32
     _launch("search_backward", _C.lib().stnls_search_backward_sm, _ptr(gq), _ptr(gk), _ptr(gflows), _ptr(q_cl),
             _ptr(k_cl), _ptr(flows if flows_grad else None), _ptr(grad_weights), _ptr(weights), float(scale),
@@ -279,11 +279,15 @@ def wpsum_forward_sm(v_cl, dists, scale, flows, counts, geom, opts):
     return out, weights
 
 
-def wpsum_backward(gout_cl, v_cl, weights, flows, geom, opts, gv_out=None):
+def wpsum_backward(gout_cl, v_cl, weights, flows, geom, opts, gv_out=None, gw_out=None, gf_out=None):
+    """*_out: optional PRE-ZEROED accumulators (views of one workspace, a symmetric-memory buffer, ...)."""
     _need_cuda(gout_cl, v_cl, weights, flows)
-    gv = th.zeros_like(v_cl) if gv_out is None else gv_out      # gv_out: pre-zeroed accumulator
-    gw = th.zeros_like(weights)
-    gf = None if opts.itype_int else th.zeros(flows.shape, device=flows.device, dtype=th.float32)
+    gv = th.zeros_like(v_cl) if gv_out is None else gv_out
+    gw = th.zeros_like(weights) if gw_out is None else gw_out
+    if opts.itype_int:
+        gf = None
+    else:
+        gf = th.zeros(flows.shape, device=flows.device, dtype=th.float32) if gf_out is None else gf_out
     _launch("wpsum_backward", _C.lib().stnls_wpsum_backward, _ptr(gv), _ptr(gw), _ptr(gf), _ptr(gout_cl), _ptr(v_cl),
                                            _ptr(weights), _ptr(flows),
                                            ctypes.byref(geom), ctypes.byref(opts), _stream())
