@@ -321,6 +321,8 @@ def run_product(args):
             host_enqueue.append(time.perf_counter() - h0)
             e1.record()
             evs.append((e0, e1))
+            for t in fresh[i]:   # the step's gradients were computed; do not keep K sets of them alive -- the caching
+                t.grad = None    # allocator would have to cudaMalloc inside the timed loop once its pool is used up
         barrier()
     launches = ops.LAUNCHES - launches0
     timeline, ops.TIMELINE = ops.TIMELINE, None
