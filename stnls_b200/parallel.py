@@ -327,7 +327,9 @@ class PeerHaloCL:
     slices lent to the neighbours (vector REDs) into the owned slice, which the unpack kernel reads in place.
     Per step: 2 copy launches and 2 handshakes (the planar exchange of PeerHalo: 5 copy launches, 2 group barriers).
     Buffers are double-buffered: a rank rewrites a buffer two exchanges after its neighbours read it, and has waited
-    for their next signal in between."""
+    for their next signal in between.  The forward pass saves VIEWS of these buffers for its backward pass, so the
+    backward of a step must run before the second-next forward (forward, backward, forward, backward ... or two steps
+    in flight at most); every rank must make the same sequence of calls."""
 
     def __init__(self, plan, group=None, timeout_ms=30000):
         import torch.distributed._symmetric_memory as symm_mem
