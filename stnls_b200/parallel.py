@@ -367,30 +367,49 @@ class PeerHaloCL:
     def pull(self, items):
         """items: [(view, hdl)] packed owned frames in place; fetch the halo frames of each from the neighbours."""
         from . import ops
-        plan = self.plan
         jobs = []
         for view, hdl in items:
             N, n_ext, frame = view.shape
-            for src, lo, hi in plan.recvs():
-                fa_s, fb_s = plan.need[src]
-                jobs.append((view.data_ptr() + (lo - plan.fa) * frame * 4,
-                             self._peer_ptr(hdl, src, N, frame) + (lo - fa_s) * frame * 4,
-                             (hi - lo) * frame, N, n_ext * frame, (fb_s - fa_s) * frame))
+            for peer, doff, soff, nfloat, rows, dpitch, spitch in halo_pull_jobs(self.plan, N, frame):
+                jobs.append((view.data_ptr() + doff * 4, self._peer_ptr(hdl, peer, N, frame) + soff * 4, nfloat, rows,
+                             dpitch, spitch))
         ops.seg_copy2d(jobs)
 
     def pull_add(self, items):
         """items: [(view, hdl)] owned + halo gradients; add what the neighbours accumulated for this rank's frames."""
         from . import ops
-        plan = self.plan
         jobs = []
         for view, hdl in items:
             N, n_ext, frame = view.shape
-            for dst, lo, hi in plan.sends():
-                fa_d, fb_d = plan.need[dst]
-                jobs.append((view.data_ptr() + (lo - plan.fa) * frame * 4,
-                             self._peer_ptr(hdl, dst, N, frame) + (lo - fa_d) * frame * 4,
-                             (hi - lo) * frame, N, n_ext * frame, (fb_d - fa_d) * frame))
+            for peer, doff, soff, nfloat, rows, dpitch, spitch in halo_pull_add_jobs(self.plan, N, frame):
+                jobs.append((view.data_ptr() + doff * 4, self._peer_ptr(hdl, peer, N, frame) + soff * 4, nfloat, rows,
+                             dpitch, spitch))
         ops.seg_copy2d(jobs, accumulate=True)
+
+
+def halo_pull_jobs(plan, N, frame):
+    """Forward halo of a channels-last video (N, n_ext, frame floats) held per rank as owned + halo frames [fa, fb):
+    [(peer, dst_offset, src_offset, nfloat, rows, dst_pitch, src_pitch)] in floats -- `rows` (= N) runs of nfloat floats
+    copied from `peer`'s buffer (whose slabs hold ITS n_ext frames) into this rank's.  Pure index math (CPU-tested)."""
+    n_ext = plan.fb - plan.fa
+    jobs = []
+    for src, lo, hi in plan.recvs():
+        fa_s, fb_s = plan.need[src]
+        jobs.append((src, (lo - plan.fa) * frame, (lo - fa_s) * frame, (hi - lo) * frame, N, n_ext * frame,
+                     (fb_s - fa_s) * frame))
+    return jobs
+
+
+def halo_pull_add_jobs(plan, N, frame):
+    """Backward: the gradient a neighbour accumulated for frames [lo, hi) this rank OWNS sits in the neighbour's owned + halo
+    gradient video; same tuple layout as halo_pull_jobs, to be ADDED into this rank's buffer."""
+    n_ext = plan.fb - plan.fa
+    jobs = []
+    for dst, lo, hi in plan.sends():
+        fa_d, fb_d = plan.need[dst]
+        jobs.append((dst, (lo - plan.fa) * frame, (lo - fa_d) * frame, (hi - lo) * frame, N, n_ext * frame,
+                     (fb_d - fa_d) * frame))
+    return jobs
 
 
 class PeerHaloExchangeMulti(th.autograd.Function):

@@ -131,3 +131,49 @@ def test_halo_exchange_inside_batch_groups_gloo():
     assert len(ret) == 4
     for r in range(4):
         assert ret[r] == (True, True), (r, ret[r])
+
+
+@pytest.mark.parametrize("T,wt,world", [(10, 2, 2), (20, 2, 4), (9, 1, 3), (40, 2, 8), (7, 3, 2), (11, 2, 5), (6, 2, 3)])
+def test_channels_last_halo_job_lists(T, wt, world):
+    """Index math of the channels-last halo exchange (parallel.PeerHaloCL) without a GPU: every rank's owned + halo buffer
+    (N, n_ext, frame) as a numpy array, the pull / pull-add job lists executed as strided copies.  Forward must
+    reproduce the slice [fa, fb) of the clip on every rank; backward must sum, into each owner, every rank's
+    gradient for the frames it lent out."""
+    import numpy as np
+    from stnls_b200 import parallel
+    N, frame = 3, 8
+    rng = np.random.default_rng(T * 100 + wt * 10 + world)
+    clip = rng.standard_normal((N, T, frame)).astype(np.float32)
+    plans = [parallel.ShardPlan(T, wt, world, r) for r in range(world)]
+
+    def run(jobs_of, bufs, accumulate):
+        out = [b.copy() for b in bufs]
+        for r, plan in enumerate(plans):
+            for peer, doff, soff, nfloat, rows, dpitch, spitch in jobs_of(plan, N, frame):
+                src, dst = bufs[peer].reshape(-1), out[r].reshape(-1)
+                for row in range(rows):
+                    seg = src[soff + row * spitch: soff + row * spitch + nfloat]
+                    if accumulate:
+                        dst[doff + row * dpitch: doff + row * dpitch + nfloat] += seg
+                    else:
+                        dst[doff + row * dpitch: doff + row * dpitch + nfloat] = seg
+        return out
+
+    # forward: owned frames packed in place, halo frames unknown (NaN) until pulled
+    bufs = []
+    for plan in plans:
+        b = np.full((N, plan.fb - plan.fa, frame), np.nan, dtype=np.float32)
+        b[:, plan.a - plan.fa: plan.b - plan.fa] = clip[:, plan.a:plan.b]
+        bufs.append(b)
+    got = run(parallel.halo_pull_jobs, bufs, False)
+    for plan, b in zip(plans, got):
+        assert np.array_equal(b, clip[:, plan.fa:plan.fb]), f"rank {plan.rank}: halo frames differ"
+    # backward: every rank holds a gradient for all of [fa, fb); owners collect the lent slices
+    grads = [rng.standard_normal((N, p.fb - p.fa, frame)).astype(np.float32) for p in plans]
+    want = np.zeros((N, T, frame), dtype=np.float64)
+    for p, g in zip(plans, grads):
+        want[:, p.fa:p.fb] += g
+    got = run(parallel.halo_pull_add_jobs, grads, True)
+    for p, b in zip(plans, got):
+        own = b[:, p.a - p.fa: p.b - p.fa]
+        assert np.allclose(own, want[:, p.a:p.b], atol=1e-5), f"rank {p.rank}: gradient of the owned frames"
